@@ -1,0 +1,514 @@
+// Darlin (L1-regularised logistic regression by block coordinate descent) on sm_100a.
+//
+// One process per GPU hosts a worker (rows of X, CSC over its local columns) and a server
+// shard (a key range of w).  The three phases of a feature-block step are
+//
+//   grad_push      K1 + C1  worker: g_j,u_j per column -> stores into the owner shard's
+//                           per-worker landing slot over NVLink peer memory, then a
+//                           release.sys flag                      (ref darlin.h:344-427)
+//   server_update  K2 + K3  server: acquire all workers' flags, reduce the slots in fixed
+//                           worker order, prox-Newton + trust region + KKT filter, publish
+//                           w / dw, release version flags         (ref darlin.h:175-246)
+//   pull_update    K4 + C2  worker: acquire the owners' version flags, load w / dw of its
+//                           columns from the owner shard in peer memory, update the
+//                           margins z_i += dw_j * y_i x_ij        (ref darlin.h:317-342,429-502)
+//
+// Differences from the reference that are deliberate:
+//   * the worker keeps the margin z_i = y_i<x_i,w> (= log dual_i) instead of dual_i, so the
+//     column scatter is an fp64 atomicAdd instead of a multiply that would race between
+//     columns of one block (the reference avoids the race by row-partitioning threads);
+//   * values are pre-multiplied by the label (sval = y_i x_ij), removing the y gather;
+//   * nothing is sent for inactive columns (the server's active set is identical, so the
+//     NaN the reference tunnels through G/U is redundant); w itself still carries the NaN
+//     mark so the worker learns about newly filtered coordinates exactly as in the reference;
+//   * the server publishes dw = w_new - w_old next to w, so all segments of a long column
+//     can be processed by independent warps without reading a half-updated cached w.
+#include "common.cuh"
+#include "../../include/psb200.h"
+
+namespace psb {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kMaxBps = 32;  // max feature blocks merged into one step (tau+1)
+
+struct StepPlan {
+  int64_t first[kMaxBps];   // first segment (worker) / first key (server) of block q
+  int64_t pref[kMaxBps + 1];
+  uint32_t mask;
+};
+
+__device__ __forceinline__ int locate(const StepPlan& p, int nb, int64_t v) {
+  int q = 0;
+  while (q + 1 < nb && v >= p.pref[q + 1]) ++q;
+  return q;
+}
+
+__device__ __forceinline__ void plan_worker(StepPlan& p, const psb_darlin_worker& W,
+                                            const int32_t* order, int step, int bps) {
+  int64_t pref = 0;
+  uint32_t mask = 0;
+  for (int q = 0; q < bps; ++q) {
+    int b = order[(int64_t)step * bps + q];
+    int64_t lo = 0, n = 0;
+    if (b >= 0) {
+      int64_t cl = W.blk_col[2 * b], ch = W.blk_col[2 * b + 1];
+      lo = W.col_seg[cl];
+      n = W.col_seg[ch] - lo;
+      mask |= W.blk_srv_mask[b];
+    }
+    p.first[q] = lo;
+    p.pref[q] = pref;
+    pref += n;
+  }
+  p.pref[bps] = pref;
+  p.mask = mask;
+}
+
+// -------------------------------------------------------------------------------------------
+// K1 + push
+// -------------------------------------------------------------------------------------------
+__device__ __forceinline__ void push_column(const psb_darlin_worker& W, int64_t j, double g,
+                                            double u) {
+  int s = W.col_owner[j];
+  int64_t at = (int64_t)W.rank * W.land_cap[s] + W.col_off[j];
+  W.land_g[s][at] = g;  // peer store when s != rank
+  W.land_u[s][at] = u;
+}
+
+template <bool BINARY>
+__global__ void __launch_bounds__(kThreads)
+k_grad_push(const __grid_constant__ psb_darlin_worker W, const psb_darlin_ctrl* __restrict__ ctrl,
+            const int32_t* __restrict__ order, int step, int bps) {
+  __shared__ StepPlan plan;
+  if (threadIdx.x == 0) plan_worker(plan, W, order, step, bps);
+  __syncthreads();
+  const int64_t total = plan.pref[bps];
+  const int lane = threadIdx.x & 31;
+  const int64_t gw = (int64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
+  const int64_t nw = (int64_t)gridDim.x * kWarps;
+
+  for (int64_t v = gw; v < total; v += nw) {
+    const int q = locate(plan, bps, v);
+    const int64_t s = plan.first[q] + (v - plan.pref[q]);
+    const int64_t j = W.seg_col[s];
+    if (!bit_test(W.active, j)) continue;
+    const int64_t cs = W.col_seg[j];
+    const int nseg = (int)(W.col_seg[j + 1] - cs);
+    const int64_t beg = W.seg_beg[s];
+    const int64_t end = min(beg + (int64_t)W.seg_len, W.col_ptr[j + 1]);
+    double d = W.delta[j];
+    if (BINARY) d = exp(d);
+    double g = 0, u = 0;
+#pragma unroll 2
+    for (int64_t e = beg + lane; e < end; e += 32) {
+      const uint32_t i = __ldg(W.row_idx + e);
+      const double zi = W.z[i];
+      // tau = 1/(1+dual) with dual = exp(z)
+      const double tau = 1.0 / (1.0 + exp(zi));
+      if (BINARY) {
+        const double yv = (double)__ldg(W.y + i);
+        g -= yv * tau;
+        u += fmin(tau * (1.0 - tau) * d, 0.25);
+      } else {
+        const double sv = (double)__ldg(W.sval + e);
+        g -= tau * sv;
+        u += fmin(tau * (1.0 - tau) * exp(fabs(sv) * d), 0.25) * sv * sv;
+      }
+    }
+    g = warp_sum(g);
+    u = warp_sum(u);
+    if (nseg == 1) {
+      if (lane == 0) push_column(W, j, g, u);
+      continue;
+    }
+    // long column: park the partial, the last arriving segment reduces in segment order
+    int old = 0;
+    if (lane == 0) {
+      __stcg(W.part + 2 * v, g);
+      __stcg(W.part + 2 * v + 1, u);
+      __threadfence();
+      old = atomicAdd(W.col_cnt + j, 1);
+    }
+    old = __shfl_sync(FULL, old, 0);
+    if (old == nseg - 1) {
+      __threadfence();
+      const int64_t v0 = v - (s - cs);
+      double sg = 0, su = 0;
+      for (int k = lane; k < nseg; k += 32) {
+        sg += __ldcg(W.part + 2 * (v0 + k));
+        su += __ldcg(W.part + 2 * (v0 + k) + 1);
+      }
+      sg = warp_sum(sg);
+      su = warp_sum(su);
+      if (lane == 0) {
+        push_column(W, j, sg, su);
+        W.col_cnt[j] = 0;
+      }
+    }
+  }
+  // all of this CTA's peer stores are ordered before its arrival; the last CTA raises flags
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    unsigned old = atomicAdd(W.done_ctr, 1u);
+    if (old == gridDim.x - 1) {
+      *W.done_ctr = 0;
+      __threadfence_system();
+      const uint64_t seq = ctrl->seq_base + (uint64_t)step + 1;
+      for (int sv = 0; sv < W.n_servers; ++sv)
+        if (plan.mask >> sv & 1u) st_release_sys(W.push_flag[sv] + W.rank, seq);
+    }
+  }
+}
+
+// -------------------------------------------------------------------------------------------
+// K2 + K3: server
+// -------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+k_server_update(const __grid_constant__ psb_darlin_server S, const psb_darlin_ctrl* __restrict__ ctrl,
+                const int32_t* __restrict__ order, int step, int bps) {
+  __shared__ StepPlan plan;
+  __shared__ double s_vio[kWarps];
+  const uint64_t seq = ctrl->seq_base + (uint64_t)step + 1;
+  if (threadIdx.x == 0) {
+    int64_t pref = 0;
+    for (int q = 0; q < bps; ++q) {
+      int b = order[(int64_t)step * bps + q];
+      int64_t lo = 0, n = 0;
+      if (b >= 0) {
+        lo = S.blk_rng[2 * b];
+        n = S.blk_rng[2 * b + 1] - lo;
+      }
+      plan.first[q] = lo;
+      plan.pref[q] = pref;
+      pref += n;
+    }
+    plan.pref[bps] = pref;
+  }
+  __syncthreads();
+  const int64_t total = plan.pref[bps];
+  if (total == 0) return;  // "none of my business" (ref darlin.h:188-189): nobody waits on us
+  if (threadIdx.x < S.n_workers) spin_until_ge(S.push_flag + threadIdx.x, seq);
+  __syncthreads();
+
+  const double lambda = ctrl->lambda, eta = ctrl->eta, delta_max = ctrl->delta_max;
+  const double thr = ctrl->kkt_threshold;
+  double vio_max = 0;
+  for (int64_t v = (int64_t)blockIdx.x * kThreads + threadIdx.x; v < total;
+       v += (int64_t)gridDim.x * kThreads) {
+    const int q = locate(plan, bps, v);
+    const int64_t k = plan.first[q] + (v - plan.pref[q]);
+    if (!bit_test(S.active, k)) continue;
+    double w = S.w[k];
+    // revived by reset_kkt_filter but still NaN: arithmetic on NaN keeps it NaN in the
+    // reference, the bit stays set there too, so only skip
+    if (is_marked(w)) continue;
+    double g = 0, u = 0;
+    for (int r = 0; r < S.n_workers; ++r) {  // fixed order => run-to-run deterministic
+      const int64_t at = (int64_t)r * S.land_cap + k;
+      g += __ldcg(S.land_g + at);  // slots of workers that lack the column stay 0 forever
+      u += __ldcg(S.land_u + at);
+    }
+    u = u / eta + 1e-10;
+    const double g_pos = g + lambda, g_neg = g - lambda;
+    double d = -w, vio = 0;
+    if (w == 0) {
+      if (g_pos < 0) {
+        vio = -g_pos;
+      } else if (g_neg > 0) {
+        vio = g_neg;
+      } else if (g_pos > thr && g_neg < -thr) {
+        bit_clear_atomic(S.active, k);
+        S.w[k] = nan_mark();
+        S.dw[k] = 0;
+        continue;
+      }
+    }
+    vio_max = fmax(vio_max, vio);
+    if (g_pos <= u * w) {
+      d = -g_pos / u;
+    } else if (g_neg >= u * w) {
+      d = -g_neg / u;
+    }
+    const double dl = S.delta[k];
+    d = fmin(dl, fmax(-dl, d));
+    S.delta[k] = fmin(delta_max, 2 * fabs(d) + .1);
+    const double w_new = w + d;
+    S.w[k] = w_new;
+    S.dw[k] = w_new - w;  // what the reference worker computes as new_w - cur_w
+  }
+  vio_max = warp_max(vio_max);
+  if ((threadIdx.x & 31) == 0) s_vio[threadIdx.x >> 5] = vio_max;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int i = 1; i < kWarps; ++i) vio_max = fmax(vio_max, s_vio[i]);
+    if (vio_max > 0) atomic_max_nonneg(S.violation, vio_max);
+    __threadfence_system();
+    unsigned old = atomicAdd(S.done_ctr, 1u);
+    if (old == gridDim.x - 1) {
+      *S.done_ctr = 0;
+      __threadfence_system();
+      for (int r = 0; r < S.n_workers; ++r) st_release_sys(S.ver_flag[r], seq);
+    }
+  }
+}
+
+// -------------------------------------------------------------------------------------------
+// K4 + pull
+// -------------------------------------------------------------------------------------------
+template <bool BINARY>
+__global__ void __launch_bounds__(kThreads)
+k_pull_update(const __grid_constant__ psb_darlin_worker W, const psb_darlin_ctrl* __restrict__ ctrl,
+              const int32_t* __restrict__ order, int step, int bps) {
+  __shared__ StepPlan plan;
+  if (threadIdx.x == 0) plan_worker(plan, W, order, step, bps);
+  __syncthreads();
+  const int64_t total = plan.pref[bps];
+  if (total == 0) return;
+  const uint64_t seq = ctrl->seq_base + (uint64_t)step + 1;
+  if (threadIdx.x < W.n_servers && (plan.mask >> threadIdx.x & 1u))
+    spin_until_ge(W.ver_flag + threadIdx.x, seq);
+  __syncthreads();
+  const double delta_max = ctrl->delta_max;
+  const int lane = threadIdx.x & 31;
+  const int64_t gw = (int64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
+  const int64_t nw = (int64_t)gridDim.x * kWarps;
+  for (int64_t v = gw; v < total; v += nw) {
+    const int q = locate(plan, bps, v);
+    const int64_t s = plan.first[q] + (v - plan.pref[q]);
+    const int64_t j = W.seg_col[s];
+    double w_new = 0, d = 0;
+    if (lane == 0) {
+      const int o = W.col_owner[j];
+      const int64_t off = W.col_off[j];
+      w_new = ld_volatile_f64(W.srv_w[o] + off);  // peer load when o != rank
+      d = ld_volatile_f64(W.srv_dw[o] + off);
+    }
+    w_new = __shfl_sync(FULL, w_new, 0);
+    d = __shfl_sync(FULL, d, 0);
+    const bool first = (s == W.col_seg[j]);
+    if (is_marked(w_new)) {  // the server filtered this coordinate (ref darlin.h:439-444)
+      if (first && lane == 0) {
+        bit_clear_atomic(W.active, j);
+        W.w[j] = 0;
+      }
+      continue;
+    }
+    if (!bit_test(W.active, j)) continue;
+    if (first && lane == 0) {
+      W.w[j] = w_new;
+      W.delta[j] = fmin(delta_max, 2 * fabs(d) + .1);
+    }
+    if (d == 0) continue;
+    const int64_t beg = W.seg_beg[s];
+    const int64_t end = min(beg + (int64_t)W.seg_len, W.col_ptr[j + 1]);
+#pragma unroll 2
+    for (int64_t e = beg + lane; e < end; e += 32) {
+      const uint32_t i = __ldg(W.row_idx + e);
+      const double sv = BINARY ? (double)__ldg(W.y + i) : (double)__ldg(W.sval + e);
+      atomicAdd(W.z + i, d * sv);  // dual_i *= exp(y_i d x_ij)  <=>  z_i += d * sval
+    }
+  }
+}
+
+// -------------------------------------------------------------------------------------------
+// pass begin, K5 evaluate
+// -------------------------------------------------------------------------------------------
+__global__ void k_pass_begin(uint32_t* wk_active, int64_t wk_cols, uint32_t* sv_active,
+                             int64_t sv_keys, double* sv_w, double* violation,
+                             const psb_darlin_ctrl* __restrict__ ctrl) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  if (t == 0 && violation) *violation = 0;
+  if (!ctrl->reset_kkt_filter) return;
+  // fill(true) but keep the padding bits of the last word clear so popcounts stay exact
+  for (int64_t i = t; i < (wk_cols + 31) / 32; i += stride) {
+    int64_t rem = wk_cols - i * 32;
+    wk_active[i] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
+  }
+  for (int64_t i = t; i < (sv_keys + 31) / 32; i += stride) {
+    int64_t rem = sv_keys - i * 32;
+    sv_active[i] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
+  }
+  if (ctrl->revive_on_reset && sv_w)
+    for (int64_t i = t; i < sv_keys; i += stride)
+      if (is_marked(sv_w[i])) sv_w[i] = 0;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_evaluate(const double* __restrict__ z, int64_t n_rows, const double* __restrict__ w,
+           const uint32_t* __restrict__ active, int64_t n_keys, const double* violation,
+           const psb_darlin_ctrl* __restrict__ ctrl, psb_darlin_progress* out_local,
+           psb_darlin_progress* const* out_peer, int n_peers, uint64_t seq, double* scratch) {
+  __shared__ double sh[4][kWarps];
+  const int64_t t = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  double loss = 0, l1 = 0;
+  unsigned long long nnz = 0, nact = 0;
+  for (int64_t i = t; i < n_rows; i += stride) {
+    const double zi = z[i];
+    // log(1 + 1/dual) = log(1+exp(-z)), evaluated without overflow
+    loss += zi > 0 ? log1p(exp(-zi)) : (-zi + log1p(exp(zi)));
+  }
+  for (int64_t i = t; i < n_keys; i += stride) {
+    const double wi = w[i];
+    if (!is_marked(wi) && wi != 0) {
+      ++nnz;
+      l1 += fabs(wi);
+    }
+  }
+  for (int64_t i = t; i < (n_keys + 31) / 32; i += stride) nact += __popc(active[i]);
+  loss = warp_sum(loss);
+  l1 = warp_sum(l1);
+  double dn = warp_sum((double)nnz), da = warp_sum((double)nact);
+  const int wid = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) {
+    sh[0][wid] = loss; sh[1][wid] = l1; sh[2][wid] = dn; sh[3][wid] = da;
+  }
+  __syncthreads();
+  uint32_t* ctr = reinterpret_cast<uint32_t*>(scratch + 4 * (int64_t)gridDim.x);
+  __shared__ bool last;
+  if (threadIdx.x == 0) {
+    for (int c = 0; c < 4; ++c) {
+      double a = 0;
+      for (int i = 0; i < kWarps; ++i) a += sh[c][i];
+      __stcg(scratch + 4 * (int64_t)blockIdx.x + c, a);
+    }
+    __threadfence();
+    last = atomicAdd(ctr, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  // fixed-order final reduction by one warp-strided pass of the last CTA
+  double acc[4] = {0, 0, 0, 0};
+  for (int b = threadIdx.x; b < gridDim.x; b += kThreads)
+    for (int c = 0; c < 4; ++c) acc[c] += __ldcg(scratch + 4 * (int64_t)b + c);
+  for (int c = 0; c < 4; ++c) acc[c] = warp_sum(acc[c]);
+  if ((threadIdx.x & 31) == 0)
+    for (int c = 0; c < 4; ++c) sh[c][wid] = acc[c];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int c = 0; c < 4; ++c) {
+      double a = 0;
+      for (int i = 0; i < kWarps; ++i) a += sh[c][i];
+      acc[c] = a;
+    }
+    *ctr = 0;
+    psb_darlin_progress p;
+    p.loss = acc[0];
+    p.penalty = acc[1] * ctrl->lambda;
+    p.nnz_w = (uint64_t)(acc[2] + 0.5);
+    p.nnz_active = (uint64_t)(acc[3] + 0.5);
+    p.violation = violation ? *violation : 0;
+    const uint64_t stamp = seq ? seq : ctrl->seq_base + (uint64_t)ctrl->n_steps;
+    p.seq = 0;
+    for (int r = -1; r < n_peers; ++r) {
+      psb_darlin_progress* o = r < 0 ? out_local : out_peer[r];
+      if (!o) continue;
+      o->loss = p.loss; o->penalty = p.penalty; o->violation = p.violation;
+      o->nnz_w = p.nnz_w; o->nnz_active = p.nnz_active;
+    }
+    __threadfence_system();
+    for (int r = -1; r < n_peers; ++r) {
+      psb_darlin_progress* o = r < 0 ? out_local : out_peer[r];
+      if (o) st_release_sys(&o->seq, stamp);
+    }
+  }
+}
+
+}  // namespace psb
+
+using namespace psb;
+
+PSB_API int psb_darlin_pass_begin(const psb_darlin_worker* wk, const psb_darlin_server* sv,
+                                  const psb_darlin_ctrl* ctrl, void* stream) {
+  PSB_REQUIRE(ctrl, "psb_darlin_pass_begin: ctrl is NULL");
+  int64_t n = 1;
+  if (wk) n = max(n, (wk->n_cols + 31) / 32);
+  if (sv) n = max(n, sv->n_keys);
+  int grid = min(div_up(n, 256), 4 * sm_count());
+  k_pass_begin<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      wk ? wk->active : nullptr, wk ? wk->n_cols : 0, sv ? sv->active : nullptr,
+      sv ? sv->n_keys : 0, sv ? sv->w : nullptr, sv ? sv->violation : nullptr, ctrl);
+  PSB_LAUNCH_CHECK();
+  return 0;
+}
+
+static int check_step_args(const char* who, int bps, int grid) {
+  PSB_REQUIRE(bps >= 1 && bps <= kMaxBps, "%s: blocks_per_step=%d outside [1,%d]", who, bps, kMaxBps);
+  PSB_REQUIRE(grid >= 1, "%s: grid=%d", who, grid);
+  return 0;
+}
+
+PSB_API int psb_darlin_grad_push(const psb_darlin_worker* wk, const psb_darlin_ctrl* ctrl,
+                                 const int32_t* order, int32_t step, int32_t bps, int32_t grid,
+                                 void* stream) {
+  PSB_REQUIRE(wk && ctrl && order, "psb_darlin_grad_push: NULL argument");
+  if (int rc = check_step_args("psb_darlin_grad_push", bps, grid)) return rc;
+  PSB_REQUIRE(wk->n_servers <= PSB_MAX_PEERS, "n_servers > PSB_MAX_PEERS");
+  if (wk->sval)
+    k_grad_push<false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(*wk, ctrl, order, step, bps);
+  else
+    k_grad_push<true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(*wk, ctrl, order, step, bps);
+  PSB_LAUNCH_CHECK();
+  return 0;
+}
+
+PSB_API int psb_darlin_server_update(const psb_darlin_server* sv, const psb_darlin_ctrl* ctrl,
+                                     const int32_t* order, int32_t step, int32_t bps,
+                                     int32_t grid, void* stream) {
+  PSB_REQUIRE(sv && ctrl && order, "psb_darlin_server_update: NULL argument");
+  if (int rc = check_step_args("psb_darlin_server_update", bps, grid)) return rc;
+  PSB_REQUIRE(sv->n_workers <= PSB_MAX_PEERS, "n_workers > PSB_MAX_PEERS");
+  k_server_update<<<grid, kThreads, 0, (cudaStream_t)stream>>>(*sv, ctrl, order, step, bps);
+  PSB_LAUNCH_CHECK();
+  return 0;
+}
+
+PSB_API int psb_darlin_pull_update(const psb_darlin_worker* wk, const psb_darlin_ctrl* ctrl,
+                                   const int32_t* order, int32_t step, int32_t bps, int32_t grid,
+                                   void* stream) {
+  PSB_REQUIRE(wk && ctrl && order, "psb_darlin_pull_update: NULL argument");
+  if (int rc = check_step_args("psb_darlin_pull_update", bps, grid)) return rc;
+  if (wk->sval)
+    k_pull_update<false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(*wk, ctrl, order, step, bps);
+  else
+    k_pull_update<true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(*wk, ctrl, order, step, bps);
+  PSB_LAUNCH_CHECK();
+  return 0;
+}
+
+PSB_API int64_t psb_darlin_evaluate_scratch_bytes(int32_t grid) {
+  return (int64_t)grid * 4 * sizeof(double) + 16;
+}
+
+PSB_API int psb_darlin_evaluate(const psb_darlin_worker* wk, const psb_darlin_server* sv,
+                                const psb_darlin_ctrl* ctrl, psb_darlin_progress* out_local,
+                                psb_darlin_progress* const* out_peer, int32_t n_peers,
+                                uint64_t seq, double* scratch, int32_t grid, void* stream) {
+  PSB_REQUIRE(ctrl && scratch && grid >= 1, "psb_darlin_evaluate: bad argument");
+  k_evaluate<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+      wk ? wk->z : nullptr, wk ? wk->n_rows : 0, sv ? sv->w : nullptr,
+      sv ? sv->active : nullptr, sv ? sv->n_keys : 0, sv ? sv->violation : nullptr, ctrl,
+      out_local, out_peer, out_peer ? n_peers : 0, seq, scratch);
+  PSB_LAUNCH_CHECK();
+  return 0;
+}
+
+PSB_API int psb_darlin_enqueue_pass(const psb_darlin_worker* wk, const psb_darlin_server* sv,
+                                    const psb_darlin_ctrl* ctrl, const int32_t* order,
+                                    int32_t n_steps, int32_t bps, int32_t grid_worker,
+                                    int32_t grid_server, psb_darlin_progress* out_local,
+                                    psb_darlin_progress* const* out_peer, int32_t n_peers,
+                                    double* eval_scratch, int32_t grid_eval, void* stream) {
+  if (int rc = psb_darlin_pass_begin(wk, sv, ctrl, stream)) return rc;
+  for (int i = 0; i < n_steps; ++i) {
+    if (wk) if (int rc = psb_darlin_grad_push(wk, ctrl, order, i, bps, grid_worker, stream)) return rc;
+    if (sv) if (int rc = psb_darlin_server_update(sv, ctrl, order, i, bps, grid_server, stream)) return rc;
+    if (wk) if (int rc = psb_darlin_pull_update(wk, ctrl, order, i, bps, grid_worker, stream)) return rc;
+  }
+  return psb_darlin_evaluate(wk, sv, ctrl, out_local, out_peer, n_peers, 0, eval_scratch,
+                             grid_eval, stream);
+}

@@ -1,0 +1,27 @@
+import os
+import sys
+
+import pytest
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    config.addinivalue_line("markers", "multigpu: needs >= 2 CUDA devices")
+
+
+def pytest_collection_modifyitems(config, items):
+    try:
+        import torch
+        have = torch.cuda.is_available()
+        ndev = torch.cuda.device_count() if have else 0
+    except Exception:  # noqa: BLE001
+        have, ndev = False, 0
+    skip_gpu = pytest.mark.skip(reason="no CUDA device")
+    skip_multi = pytest.mark.skip(reason="needs >= 2 CUDA devices")
+    for it in items:
+        if "gpu" in it.keywords and not have:
+            it.add_marker(skip_gpu)
+        if "multigpu" in it.keywords and ndev < 2:
+            it.add_marker(skip_multi)
