@@ -92,6 +92,7 @@ def main() -> None:
     ap.add_argument("--block-ratio", type=float, default=4.0)
     ap.add_argument("--seg-len", type=int, default=256)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--split", action="store_true", help="3 kernels per step instead of the persistent pass kernel")
     args = ap.parse_args()
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) == 0:
@@ -119,7 +120,7 @@ def main() -> None:
 
     cfg = DarlinConfig(lambda_l1=1.0, eta=1.0, max_pass_of_data=args.steps + args.warmup,
                        epsilon=0.0, feature_block_ratio=args.block_ratio,
-                       max_block_delay=args.tau, seg_len=args.seg_len, use_graph=not args.no_graph)
+                       max_block_delay=args.tau, seg_len=args.seg_len, use_graph=not args.no_graph, fused=not args.split)
     t0 = time.time()
     data = make_rcv1_like(args.rows, args.features, args.nnz_per_row, seed=0, shard=rank, device=dev)
     eng = DarlinEngine(cfg, comm, dev, out=sys.stderr)
@@ -184,6 +185,7 @@ def main() -> None:
                        "examples_per_gpu": args.rows, "global_examples": n_ex,
                        "features": args.features, "nnz_per_gpu": nnz,
                        "feature_blocks": len(eng.blocks), "max_block_delay": args.tau,
+                       "kernel": "split (3 launches/step)" if args.split else "persistent cooperative pass kernel",
                        "lambda": 1.0, "parallelism": f"dp{world} workers x {world} key-range server shards",
                        "l2": "inputs larger than L2 (CSC index+value arrays %.0f MB per GPU)" % (nnz * 8 / 1e6),
                        "timing": "value: CUDA events around the kernels of each pass (graph replay), summed, max over ranks; e2e: wall clock incl. host scheduler, pinned H2D, D2H, sync",

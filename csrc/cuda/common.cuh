@@ -80,6 +80,26 @@ __device__ __forceinline__ double ld_volatile_f64(const double* p) {
   asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
   return v;
 }
+// GPU-scope release/acquire used by the grid barrier of the persistent kernels
+__device__ __forceinline__ void red_release_gpu_add(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// Split grid barrier (all CTAs must be co-resident: cooperative launch).  arrive() publishes
+// every prior write of the CTA, wait() makes every other CTA's pre-arrive writes visible.
+__device__ __forceinline__ void grid_arrive(uint32_t* ctr) {
+  __syncthreads();
+  if (threadIdx.x == 0) red_release_gpu_add(ctr, 1u);
+}
+__device__ __forceinline__ void grid_wait(const uint32_t* ctr, uint32_t target) {
+  if (threadIdx.x == 0)
+    while (ld_acquire_gpu(ctr) < target) {}
+  __syncthreads();
+}
 __device__ __forceinline__ void spin_until_ge(const uint64_t* flag, uint64_t want) {
   while (ld_acquire_sys(flag) < want) { __nanosleep(20); }
 }
@@ -90,6 +110,9 @@ __device__ __forceinline__ bool is_marked(double v) { return v != v; }
 
 __device__ __forceinline__ bool bit_test(const uint32_t* bm, int64_t i) {
   return (bm[i >> 5] >> (i & 31)) & 1u;
+}
+__device__ __forceinline__ bool bit_test_cg(const uint32_t* bm, int64_t i) {  // L2-coherent read
+  return (__ldcg(bm + (i >> 5)) >> (i & 31)) & 1u;
 }
 __device__ __forceinline__ void bit_clear_atomic(uint32_t* bm, int64_t i) {
   atomicAnd(&bm[i >> 5], ~(1u << (i & 31)));

@@ -77,33 +77,25 @@ __device__ __forceinline__ void push_column(const psb_darlin_worker& W, int64_t 
 }
 
 template <bool BINARY>
-__global__ void __launch_bounds__(kThreads)
-k_grad_push(const __grid_constant__ psb_darlin_worker W, const psb_darlin_ctrl* __restrict__ ctrl,
-            const int32_t* __restrict__ order, int step, int bps) {
-  __shared__ StepPlan plan;
-  if (threadIdx.x == 0) plan_worker(plan, W, order, step, bps);
-  __syncthreads();
+__device__ __forceinline__ void grad_phase(const psb_darlin_worker& W, const StepPlan& plan, int bps,
+                                           int64_t gw, int64_t nw, int lane) {
   const int64_t total = plan.pref[bps];
-  const int lane = threadIdx.x & 31;
-  const int64_t gw = (int64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
-  const int64_t nw = (int64_t)gridDim.x * kWarps;
-
   for (int64_t v = gw; v < total; v += nw) {
     const int q = locate(plan, bps, v);
     const int64_t s = plan.first[q] + (v - plan.pref[q]);
     const int64_t j = W.seg_col[s];
-    if (!bit_test(W.active, j)) continue;
+    if (!bit_test_cg(W.active, j)) continue;
     const int64_t cs = W.col_seg[j];
     const int nseg = (int)(W.col_seg[j + 1] - cs);
     const int64_t beg = W.seg_beg[s];
     const int64_t end = min(beg + (int64_t)W.seg_len, W.col_ptr[j + 1]);
-    double d = W.delta[j];
+    double d = __ldcg(W.delta + j);
     if (BINARY) d = exp(d);
     double g = 0, u = 0;
 #pragma unroll 2
     for (int64_t e = beg + lane; e < end; e += 32) {
       const uint32_t i = __ldg(W.row_idx + e);
-      const double zi = W.z[i];
+      const double zi = __ldcg(W.z + i);
       // tau = 1/(1+dual) with dual = exp(z)
       const double tau = 1.0 / (1.0 + exp(zi));
       if (BINARY) {
@@ -147,6 +139,17 @@ k_grad_push(const __grid_constant__ psb_darlin_worker W, const psb_darlin_ctrl* 
       }
     }
   }
+}
+
+template <bool BINARY>
+__global__ void __launch_bounds__(kThreads)
+k_grad_push(const __grid_constant__ psb_darlin_worker W, const psb_darlin_ctrl* __restrict__ ctrl,
+            const int32_t* __restrict__ order, int step, int bps) {
+  __shared__ StepPlan plan;
+  if (threadIdx.x == 0) plan_worker(plan, W, order, step, bps);
+  __syncthreads();
+  grad_phase<BINARY>(W, plan, bps, (int64_t)blockIdx.x * kWarps + (threadIdx.x >> 5),
+                     (int64_t)gridDim.x * kWarps, threadIdx.x & 31);
   // all of this CTA's peer stores are ordered before its arrival; the last CTA raises flags
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -165,42 +168,21 @@ k_grad_push(const __grid_constant__ psb_darlin_worker W, const psb_darlin_ctrl* 
 // -------------------------------------------------------------------------------------------
 // K2 + K3: server
 // -------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads)
-k_server_update(const __grid_constant__ psb_darlin_server S, const psb_darlin_ctrl* __restrict__ ctrl,
-                const int32_t* __restrict__ order, int step, int bps) {
-  __shared__ StepPlan plan;
-  __shared__ double s_vio[kWarps];
-  const uint64_t seq = ctrl->seq_base + (uint64_t)step + 1;
-  if (threadIdx.x == 0) {
-    int64_t pref = 0;
-    for (int q = 0; q < bps; ++q) {
-      int b = order[(int64_t)step * bps + q];
-      int64_t lo = 0, n = 0;
-      if (b >= 0) {
-        lo = S.blk_rng[2 * b];
-        n = S.blk_rng[2 * b + 1] - lo;
-      }
-      plan.first[q] = lo;
-      plan.pref[q] = pref;
-      pref += n;
-    }
-    plan.pref[bps] = pref;
-  }
-  __syncthreads();
-  const int64_t total = plan.pref[bps];
-  if (total == 0) return;  // "none of my business" (ref darlin.h:188-189): nobody waits on us
-  if (threadIdx.x < S.n_workers) spin_until_ge(S.push_flag + threadIdx.x, seq);
-  __syncthreads();
+struct ServerHyper {
+  double lambda, eta, delta_max, thr;
+};
 
-  const double lambda = ctrl->lambda, eta = ctrl->eta, delta_max = ctrl->delta_max;
-  const double thr = ctrl->kkt_threshold;
+// thread-strided over the step's coordinates; returns this thread's max violation
+__device__ __forceinline__ double server_phase(const psb_darlin_server& S, const ServerHyper& h,
+                                               const StepPlan& plan, int bps, int64_t tid,
+                                               int64_t nthreads) {
+  const int64_t total = plan.pref[bps];
   double vio_max = 0;
-  for (int64_t v = (int64_t)blockIdx.x * kThreads + threadIdx.x; v < total;
-       v += (int64_t)gridDim.x * kThreads) {
+  for (int64_t v = tid; v < total; v += nthreads) {
     const int q = locate(plan, bps, v);
     const int64_t k = plan.first[q] + (v - plan.pref[q]);
-    if (!bit_test(S.active, k)) continue;
-    double w = S.w[k];
+    if (!bit_test_cg(S.active, k)) continue;
+    double w = __ldcg(S.w + k);
     // revived by reset_kkt_filter but still NaN: arithmetic on NaN keeps it NaN in the
     // reference, the bit stays set there too, so only skip
     if (is_marked(w)) continue;
@@ -210,15 +192,15 @@ k_server_update(const __grid_constant__ psb_darlin_server S, const psb_darlin_ct
       g += __ldcg(S.land_g + at);  // slots of workers that lack the column stay 0 forever
       u += __ldcg(S.land_u + at);
     }
-    u = u / eta + 1e-10;
-    const double g_pos = g + lambda, g_neg = g - lambda;
+    u = u / h.eta + 1e-10;
+    const double g_pos = g + h.lambda, g_neg = g - h.lambda;
     double d = -w, vio = 0;
     if (w == 0) {
       if (g_pos < 0) {
         vio = -g_pos;
       } else if (g_neg > 0) {
         vio = g_neg;
-      } else if (g_pos > thr && g_neg < -thr) {
+      } else if (g_pos > h.thr && g_neg < -h.thr) {
         bit_clear_atomic(S.active, k);
         S.w[k] = nan_mark();
         S.dw[k] = 0;
@@ -231,13 +213,48 @@ k_server_update(const __grid_constant__ psb_darlin_server S, const psb_darlin_ct
     } else if (g_neg >= u * w) {
       d = -g_neg / u;
     }
-    const double dl = S.delta[k];
+    const double dl = __ldcg(S.delta + k);
     d = fmin(dl, fmax(-dl, d));
-    S.delta[k] = fmin(delta_max, 2 * fabs(d) + .1);
+    S.delta[k] = fmin(h.delta_max, 2 * fabs(d) + .1);
     const double w_new = w + d;
     S.w[k] = w_new;
     S.dw[k] = w_new - w;  // what the reference worker computes as new_w - cur_w
   }
+  return vio_max;
+}
+
+__device__ __forceinline__ void plan_server(StepPlan& p, const psb_darlin_server& S,
+                                            const int32_t* order, int step, int bps) {
+  int64_t pref = 0;
+  for (int q = 0; q < bps; ++q) {
+    int b = order[(int64_t)step * bps + q];
+    int64_t lo = 0, n = 0;
+    if (b >= 0) {
+      lo = S.blk_rng[2 * b];
+      n = S.blk_rng[2 * b + 1] - lo;
+    }
+    p.first[q] = lo;
+    p.pref[q] = pref;
+    pref += n;
+  }
+  p.pref[bps] = pref;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_server_update(const __grid_constant__ psb_darlin_server S, const psb_darlin_ctrl* __restrict__ ctrl,
+                const int32_t* __restrict__ order, int step, int bps) {
+  __shared__ StepPlan plan;
+  __shared__ double s_vio[kWarps];
+  const uint64_t seq = ctrl->seq_base + (uint64_t)step + 1;
+  if (threadIdx.x == 0) plan_server(plan, S, order, step, bps);
+  __syncthreads();
+  const int64_t total = plan.pref[bps];
+  if (total == 0) return;  // "none of my business" (ref darlin.h:188-189): nobody waits on us
+  if (threadIdx.x < S.n_workers) spin_until_ge(S.push_flag + threadIdx.x, seq);
+  __syncthreads();
+  const ServerHyper h{ctrl->lambda, ctrl->eta, ctrl->delta_max, ctrl->kkt_threshold};
+  double vio_max = server_phase(S, h, plan, bps, (int64_t)blockIdx.x * kThreads + threadIdx.x,
+                                (int64_t)gridDim.x * kThreads);
   vio_max = warp_max(vio_max);
   if ((threadIdx.x & 31) == 0) s_vio[threadIdx.x >> 5] = vio_max;
   __syncthreads();
@@ -258,22 +275,9 @@ k_server_update(const __grid_constant__ psb_darlin_server S, const psb_darlin_ct
 // K4 + pull
 // -------------------------------------------------------------------------------------------
 template <bool BINARY>
-__global__ void __launch_bounds__(kThreads)
-k_pull_update(const __grid_constant__ psb_darlin_worker W, const psb_darlin_ctrl* __restrict__ ctrl,
-              const int32_t* __restrict__ order, int step, int bps) {
-  __shared__ StepPlan plan;
-  if (threadIdx.x == 0) plan_worker(plan, W, order, step, bps);
-  __syncthreads();
+__device__ __forceinline__ void pull_phase(const psb_darlin_worker& W, const StepPlan& plan, int bps,
+                                           double delta_max, int64_t gw, int64_t nw, int lane) {
   const int64_t total = plan.pref[bps];
-  if (total == 0) return;
-  const uint64_t seq = ctrl->seq_base + (uint64_t)step + 1;
-  if (threadIdx.x < W.n_servers && (plan.mask >> threadIdx.x & 1u))
-    spin_until_ge(W.ver_flag + threadIdx.x, seq);
-  __syncthreads();
-  const double delta_max = ctrl->delta_max;
-  const int lane = threadIdx.x & 31;
-  const int64_t gw = (int64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
-  const int64_t nw = (int64_t)gridDim.x * kWarps;
   for (int64_t v = gw; v < total; v += nw) {
     const int q = locate(plan, bps, v);
     const int64_t s = plan.first[q] + (v - plan.pref[q]);
@@ -295,7 +299,7 @@ k_pull_update(const __grid_constant__ psb_darlin_worker W, const psb_darlin_ctrl
       }
       continue;
     }
-    if (!bit_test(W.active, j)) continue;
+    if (!bit_test_cg(W.active, j)) continue;
     if (first && lane == 0) {
       W.w[j] = w_new;
       W.delta[j] = fmin(delta_max, 2 * fabs(d) + .1);
@@ -310,6 +314,23 @@ k_pull_update(const __grid_constant__ psb_darlin_worker W, const psb_darlin_ctrl
       atomicAdd(W.z + i, d * sv);  // dual_i *= exp(y_i d x_ij)  <=>  z_i += d * sval
     }
   }
+}
+
+template <bool BINARY>
+__global__ void __launch_bounds__(kThreads)
+k_pull_update(const __grid_constant__ psb_darlin_worker W, const psb_darlin_ctrl* __restrict__ ctrl,
+              const int32_t* __restrict__ order, int step, int bps) {
+  __shared__ StepPlan plan;
+  if (threadIdx.x == 0) plan_worker(plan, W, order, step, bps);
+  __syncthreads();
+  const int64_t total = plan.pref[bps];
+  if (total == 0) return;
+  const uint64_t seq = ctrl->seq_base + (uint64_t)step + 1;
+  if (threadIdx.x < W.n_servers && (plan.mask >> threadIdx.x & 1u))
+    spin_until_ge(W.ver_flag + threadIdx.x, seq);
+  __syncthreads();
+  pull_phase<BINARY>(W, plan, bps, ctrl->delta_max, (int64_t)blockIdx.x * kWarps + (threadIdx.x >> 5),
+                     (int64_t)gridDim.x * kWarps, threadIdx.x & 31);
 }
 
 // -------------------------------------------------------------------------------------------
@@ -418,6 +439,189 @@ k_evaluate(const double* __restrict__ z, int64_t n_rows, const double* __restric
   }
 }
 
+
+// -------------------------------------------------------------------------------------------
+// Persistent whole-pass kernel (cooperative launch, every CTA resident)
+//
+// One launch runs pass_begin, all steps and the progress evaluation.  The three phases of a
+// step are separated by split grid barriers (arrive / wait on one L2 counter) instead of
+// kernel boundaries; the next step's plan is fetched between arrive and wait.  Cross-GPU
+// ordering is unchanged: after barrier A one thread raises the push flags on the remote
+// owners, the server CTAs acquire the remote workers' flags before reducing, after barrier B
+// one thread raises the version flags, and the pull phase acquires the remote owners' flags.
+// With one rank no system-scope operation is executed at all.
+//
+// blk_tab[b] = {first segment, #segments, first shard key, #shard keys, server mask, 0}
+// -------------------------------------------------------------------------------------------
+struct FusedPlan {
+  StepPlan wk;   // segments
+  StepPlan sv;   // shard coordinates
+};
+
+__device__ __forceinline__ void fused_plan(FusedPlan& P, const int64_t* __restrict__ blk_tab,
+                                           const int32_t* __restrict__ order, int step, int bps) {
+  // executed by warp 0: lane q fetches block q of the step, then a warp scan builds prefixes
+  const int lane = threadIdx.x & 31;
+  int64_t seg_lo = 0, nseg = 0, key_lo = 0, nkey = 0;
+  uint32_t mask = 0;
+  if (lane < bps) {
+    const int b = __ldcg(order + (int64_t)step * bps + lane);
+    if (b >= 0) {
+      const int64_t* t = blk_tab + 6 * (int64_t)b;
+      seg_lo = __ldg(t); nseg = __ldg(t + 1); key_lo = __ldg(t + 2); nkey = __ldg(t + 3);
+      mask = (uint32_t)__ldg(t + 4);
+    }
+  }
+  int64_t ps = nseg, pk = nkey;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int64_t a = __shfl_up_sync(FULL, ps, o), c = __shfl_up_sync(FULL, pk, o);
+    if (lane >= o) { ps += a; pk += c; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mask |= __shfl_xor_sync(FULL, mask, o);
+  if (lane < bps) {
+    P.wk.first[lane] = seg_lo; P.wk.pref[lane] = ps - nseg;
+    P.sv.first[lane] = key_lo; P.sv.pref[lane] = pk - nkey;
+  }
+  if (lane == bps - 1) { P.wk.pref[bps] = ps; P.sv.pref[bps] = pk; }
+  if (lane == 0) { P.wk.mask = mask; P.sv.mask = mask; }
+}
+
+template <bool BINARY>
+__global__ void __launch_bounds__(kThreads, 2)
+k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant__ psb_darlin_server S,
+              const psb_darlin_ctrl* __restrict__ ctrl, const int32_t* __restrict__ order,
+              const int64_t* __restrict__ blk_tab, int n_steps, int bps, uint32_t* bar,
+              psb_darlin_progress* out_local, psb_darlin_progress* const* out_peer, int n_peers,
+              double* scratch) {
+  __shared__ FusedPlan plans[2];
+  __shared__ double sh[4][kWarps];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int64_t gw = (int64_t)blockIdx.x * kWarps + wid, nw = (int64_t)gridDim.x * kWarps;
+  const int64_t gt = (int64_t)blockIdx.x * kThreads + threadIdx.x, nt = (int64_t)gridDim.x * kThreads;
+  const uint32_t G = gridDim.x;
+  uint32_t nbar = 0;
+  const bool multi = W.n_workers > 1;
+  const ServerHyper h{ctrl->lambda, ctrl->eta, ctrl->delta_max, ctrl->kkt_threshold};
+  const uint64_t seq_base = ctrl->seq_base;
+
+  // ---- pass begin (ref darlin.h:176-182, 297-300) ----
+  if (gt == 0) *S.violation = 0;
+  if (ctrl->reset_kkt_filter) {
+    for (int64_t i = gt; i < (W.n_cols + 31) / 32; i += nt) {
+      const int64_t rem = W.n_cols - i * 32;
+      W.active[i] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
+    }
+    for (int64_t i = gt; i < (S.n_keys + 31) / 32; i += nt) {
+      const int64_t rem = S.n_keys - i * 32;
+      S.active[i] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
+    }
+    if (ctrl->revive_on_reset)
+      for (int64_t i = gt; i < S.n_keys; i += nt)
+        if (is_marked(__ldcg(S.w + i))) S.w[i] = 0;
+  }
+  if (wid == 0 && n_steps > 0) fused_plan(plans[0], blk_tab, order, 0, bps);
+  grid_arrive(bar);
+  grid_wait(bar, ++nbar * G);
+
+  for (int step = 0; step < n_steps; ++step) {
+    const FusedPlan& P = plans[step & 1];
+    const uint64_t seq = seq_base + (uint64_t)step + 1;
+    // ---- phase 1: gradient + push ----
+    grad_phase<BINARY>(W, P.wk, bps, gw, nw, lane);
+    grid_arrive(bar);
+    if (wid == 0 && step + 1 < n_steps) fused_plan(plans[(step + 1) & 1], blk_tab, order, step + 1, bps);
+    grid_wait(bar, ++nbar * G);
+    if (multi && blockIdx.x == G - 1 && threadIdx.x < W.n_servers && threadIdx.x != W.rank &&
+        (P.wk.mask >> threadIdx.x & 1u)) {
+      __threadfence_system();
+      st_release_sys(W.push_flag[threadIdx.x] + W.rank, seq);
+    }
+    // ---- phase 2: server update on the first CTAs ----
+    const int64_t nkeys = P.sv.pref[bps];
+    double vio = 0;
+    if (nkeys > 0 && (int64_t)blockIdx.x * kThreads < nkeys) {
+      if (multi) {
+        if (threadIdx.x < S.n_workers && threadIdx.x != S.rank)
+          spin_until_ge(S.push_flag + threadIdx.x, seq);
+        __syncthreads();
+      }
+      const int64_t ncta = min((int64_t)G, (nkeys + kThreads - 1) / kThreads);
+      vio = server_phase(S, h, P.sv, bps, gt, ncta * kThreads);
+      vio = warp_max(vio);
+      if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
+    }
+    grid_arrive(bar);
+    grid_wait(bar, ++nbar * G);
+    if (multi && nkeys > 0 && blockIdx.x == G - 1 && threadIdx.x < S.n_workers &&
+        threadIdx.x != S.rank) {
+      __threadfence_system();
+      st_release_sys(S.ver_flag[threadIdx.x], seq);
+    }
+    // ---- phase 3: pull + margin update ----
+    if (multi && P.wk.pref[bps] > 0) {
+      if (threadIdx.x < W.n_servers && threadIdx.x != W.rank && (P.wk.mask >> threadIdx.x & 1u))
+        spin_until_ge(W.ver_flag + threadIdx.x, seq);
+      __syncthreads();
+    }
+    pull_phase<BINARY>(W, P.wk, bps, h.delta_max, gw, nw, lane);
+    grid_arrive(bar);
+    grid_wait(bar, ++nbar * G);
+  }
+
+  // ---- evaluate (ref darlin.h:248-265, 504-511) ----
+  double loss = 0, l1 = 0, dn = 0, da = 0;
+  for (int64_t i = gt; i < W.n_rows; i += nt) {
+    const double zi = __ldcg(W.z + i);
+    loss += zi > 0 ? log1p(exp(-zi)) : (-zi + log1p(exp(zi)));
+  }
+  for (int64_t i = gt; i < S.n_keys; i += nt) {
+    const double wi = __ldcg(S.w + i);
+    if (!is_marked(wi) && wi != 0) { dn += 1; l1 += fabs(wi); }
+  }
+  for (int64_t i = gt; i < (S.n_keys + 31) / 32; i += nt) da += __popc(__ldcg(S.active + i));
+  loss = warp_sum(loss); l1 = warp_sum(l1); dn = warp_sum(dn); da = warp_sum(da);
+  if (lane == 0) { sh[0][wid] = loss; sh[1][wid] = l1; sh[2][wid] = dn; sh[3][wid] = da; }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    double a = 0;
+    for (int i = 0; i < kWarps; ++i) a += sh[threadIdx.x][i];
+    __stcg(scratch + 4 * (int64_t)blockIdx.x + threadIdx.x, a);
+  }
+  grid_arrive(bar);
+  if (blockIdx.x != 0) return;
+  grid_wait(bar, ++nbar * G);
+  double acc[4] = {0, 0, 0, 0};
+  for (int b = threadIdx.x; b < (int)G; b += kThreads)
+    for (int c = 0; c < 4; ++c) acc[c] += __ldcg(scratch + 4 * (int64_t)b + c);
+  for (int c = 0; c < 4; ++c) acc[c] = warp_sum(acc[c]);
+  if (lane == 0)
+    for (int c = 0; c < 4; ++c) sh[c][wid] = acc[c];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int c = 0; c < 4; ++c) {
+      double a = 0;
+      for (int i = 0; i < kWarps; ++i) a += sh[c][i];
+      acc[c] = a;
+    }
+    *bar = 0;  // every CTA has arrived at the last barrier; nobody reads the counter again
+    const double vio = __ldcg(S.violation);
+    const uint64_t stamp = seq_base + (uint64_t)n_steps;
+    for (int r = -1; r < n_peers; ++r) {
+      psb_darlin_progress* o = r < 0 ? out_local : out_peer[r];
+      if (!o) continue;
+      o->loss = acc[0]; o->penalty = acc[1] * h.lambda; o->violation = vio;
+      o->nnz_w = (uint64_t)(acc[2] + 0.5); o->nnz_active = (uint64_t)(acc[3] + 0.5);
+    }
+    if (n_peers > 0) __threadfence_system();
+    for (int r = -1; r < n_peers; ++r) {
+      psb_darlin_progress* o = r < 0 ? out_local : out_peer[r];
+      if (o) st_release_sys(&o->seq, stamp);
+    }
+  }
+}
+
 }  // namespace psb
 
 using namespace psb;
@@ -511,4 +715,35 @@ PSB_API int psb_darlin_enqueue_pass(const psb_darlin_worker* wk, const psb_darli
   }
   return psb_darlin_evaluate(wk, sv, ctrl, out_local, out_peer, n_peers, 0, eval_scratch,
                              grid_eval, stream);
+}
+
+// Whole pass in ONE cooperative launch (see k_darlin_pass).  `bar` is a zero-initialised
+// uint32 in device memory owned by the caller; `grid` must not exceed
+// psb_darlin_fused_max_grid() so that all CTAs are co-resident.
+PSB_API int psb_darlin_fused_max_grid(int32_t binary) {
+  int per_sm = 0;
+  cudaError_t e = binary
+      ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_darlin_pass<true>, kThreads, 0)
+      : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_darlin_pass<false>, kThreads, 0);
+  if (e != cudaSuccess || per_sm < 1) return 0;
+  return per_sm * sm_count();
+}
+
+PSB_API int psb_darlin_fused_pass(const psb_darlin_worker* wk, const psb_darlin_server* sv,
+                                  const psb_darlin_ctrl* ctrl, const int32_t* order,
+                                  const int64_t* blk_tab, int32_t n_steps, int32_t bps,
+                                  int32_t grid, uint32_t* bar, psb_darlin_progress* out_local,
+                                  psb_darlin_progress* const* out_peer, int32_t n_peers,
+                                  double* scratch, void* stream) {
+  PSB_REQUIRE(wk && sv && ctrl && order && blk_tab && bar && scratch, "psb_darlin_fused_pass: NULL argument");
+  if (int rc = check_step_args("psb_darlin_fused_pass", bps, grid)) return rc;
+  PSB_REQUIRE(grid <= psb_darlin_fused_max_grid(wk->sval == nullptr),
+              "psb_darlin_fused_pass: grid=%d exceeds the co-resident maximum", grid);
+  int np = out_peer ? n_peers : 0;
+  void* args[] = {(void*)wk, (void*)sv, (void*)&ctrl, (void*)&order, (void*)&blk_tab, (void*)&n_steps,
+                  (void*)&bps, (void*)&bar, (void*)&out_local, (void*)&out_peer, (void*)&np,
+                  (void*)&scratch};
+  const void* fn = wk->sval ? (const void*)k_darlin_pass<false> : (const void*)k_darlin_pass<true>;
+  PSB_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), args, 0, (cudaStream_t)stream));
+  return 0;
 }

@@ -55,6 +55,7 @@ class DarlinConfig:
     revive_on_reset: bool = False
     seed: int = 0
     use_graph: bool = True
+    fused: bool = True                # one persistent cooperative kernel per pass
 
     @staticmethod
     def from_proto(conf) -> "DarlinConfig":
@@ -271,6 +272,16 @@ class DarlinEngine:
                         blk_rng[2 * b], blk_rng[2 * b + 1] = base + a - lo, base + z - lo
                         max_blk_keys = max(max_blk_keys, z - a)
             blk_mask[b] = mask
+        cs = self.col_seg.cpu()
+        blk_tab = torch.zeros(max(nb, 1) * 6, dtype=torch.int64)
+        for b in range(nb):
+            lo, hi = int(blk_col[2 * b]), int(blk_col[2 * b + 1])
+            blk_tab[6 * b + 0] = cs[lo]
+            blk_tab[6 * b + 1] = cs[hi] - cs[lo]
+            blk_tab[6 * b + 2] = blk_rng[2 * b]
+            blk_tab[6 * b + 3] = blk_rng[2 * b + 1] - blk_rng[2 * b]
+            blk_tab[6 * b + 4] = int(blk_mask[b])
+        self.blk_tab = blk_tab.to(dev)
         self.blk_col, self.blk_rng = blk_col.to(dev), blk_rng.to(dev)
         self.blk_srv_mask = blk_mask.to(dev)
         self.max_blk_keys = max_blk_keys
@@ -310,7 +321,10 @@ class DarlinEngine:
         self.grid_worker = int(max(1, min(math.ceil(self.bps * self.max_blk_segs / 8), sm * 8)))
         self.grid_server = int(max(1, min(math.ceil(self.bps * self.max_blk_keys / 256), sm)))
         self.grid_eval = int(sm * 2)
-        self.eval_scratch = torch.zeros(K.evaluate_scratch_bytes(self.grid_eval) // 8 + 2, **f64)
+        self.grid_fused = K.fused_max_grid(self.sval is None) if cfg.fused else 0
+        self.bar = torch.zeros(4, dtype=torch.int32, device=dev)
+        self.eval_scratch = torch.zeros(
+            K.evaluate_scratch_bytes(max(self.grid_eval, 4 * sm)) // 8 + 2, **f64)
         # host-pinned staging for the per-pass inputs / result
         max_steps = len(self.blocks) + len(self.prior_blk_order) + 1
         self.order_host = torch.full((max_steps * self.bps,), -1, dtype=torch.int32).pin_memory()
@@ -377,15 +391,25 @@ class DarlinEngine:
     # one pass
     # ----------------------------------------------------------------------------------------
     def _enqueue(self, n_steps: int) -> None:
+        if self.cfg.fused and self.grid_fused > 0:
+            K.fused_pass(self.wk, self.sv, self.ctrl_dev.data_ptr(), self.order_dev.data_ptr(),
+                         self.blk_tab.data_ptr(), n_steps, self.bps, self.grid_fused,
+                         self.bar.data_ptr(),
+                         self.arena.peer_ptr(self.rank, self.b_progress, 6 * self.rank),
+                         self.prog_peer.data_ptr(), self.world, self.eval_scratch.data_ptr())
+        else:
+            self._enqueue_split(n_steps)
+        if self.world > 1:
+            from .._lib import check, cuda_lib, current_stream
+            check(cuda_lib().psb_rank_barrier_dev(self.bar_peers, self.rank, self.world,
+                                                  self.epoch_dev.data_ptr(), current_stream()))
+
+    def _enqueue_split(self, n_steps: int) -> None:
         K.enqueue_pass(self.wk, self.sv, self.ctrl_dev.data_ptr(), self.order_dev.data_ptr(),
                        n_steps, self.bps, self.grid_worker, self.grid_server,
                        self.arena.peer_ptr(self.rank, self.b_progress, 6 * self.rank),
                        self.prog_peer.data_ptr(), self.world, self.eval_scratch.data_ptr(),
                        self.grid_eval)
-        if self.world > 1:
-            from .._lib import check, cuda_lib, current_stream
-            check(cuda_lib().psb_rank_barrier_dev(self.bar_peers, self.rank, self.world,
-                                                  self.epoch_dev.data_ptr(), current_stream()))
 
     def plan_steps(self, order: list, n_prior: int = 0) -> list:
         """Group the block order into steps of <= tau+1 blocks; prior blocks run alone
@@ -418,7 +442,8 @@ class DarlinEngine:
         """Merge the progress records of all ranks (already copied to pinned host memory)."""
         self._seq += n_steps
         self._pass_index += 1
-        self.launches_per_pass = 2 + 3 * n_steps + (1 if self.world > 1 else 0)
+        fused = self.cfg.fused and self.grid_fused > 0
+        self.launches_per_pass = (1 if fused else 2 + 3 * n_steps) + (1 if self.world > 1 else 0)
         self.d2h_bytes_per_pass = self.prog_host.numel() * 8
         p = Progress()
         raw = self.prog_host.numpy()

@@ -86,3 +86,14 @@ def enqueue_pass(wk, sv, ctrl_ptr: int, order_ptr: int, n_steps: int, bps: int, 
     check(_lib().psb_darlin_enqueue_pass(_ref(wk), _ref(sv), ctrl_ptr, order_ptr, n_steps, bps,
                                          grid_w, grid_s, out_local, out_peer, n_peers,
                                          scratch_ptr, grid_eval, current_stream()))
+
+
+def fused_max_grid(binary: bool) -> int:
+    return int(_lib().psb_darlin_fused_max_grid(int(binary)))
+
+
+def fused_pass(wk, sv, ctrl_ptr: int, order_ptr: int, blk_tab_ptr: int, n_steps: int, bps: int,
+               grid: int, bar_ptr: int, out_local: int, out_peer, n_peers: int, scratch_ptr: int):
+    check(_lib().psb_darlin_fused_pass(_ref(wk), _ref(sv), ctrl_ptr, order_ptr, blk_tab_ptr,
+                                       n_steps, bps, grid, bar_ptr, out_local, out_peer, n_peers,
+                                       scratch_ptr, current_stream()))

@@ -27,14 +27,15 @@ def _oracle_from_csr(data, dictionary, device):
     return DarlinOracle(col_ptr, row, val, data.y.to(device), n_rows)
 
 
-def _run_compare(world, binary, tau, passes=4, n_rows=3000, n_feat=700, lam=0.5, tail=0, seed=3):
+def _run_compare(world, binary, tau, passes=4, n_rows=3000, n_feat=700, lam=0.5, tail=0, seed=3,
+                 fused=False, graph=False, expect_filter=True):
     from parameter_server_b200.models.darlin import DarlinConfig, DarlinEngine, run_pass_lockstep
     from parameter_server_b200.models.darlin_oracle import OracleServer, run_oracle_pass
     from parameter_server_b200.parallel.comm import run_threads
     from parameter_server_b200.utils.synthetic import make_rcv1_like
     dev = torch.device("cuda:0")
     cfg = DarlinConfig(lambda_l1=lam, max_block_delay=tau, tail_feature_freq=tail,
-                       feature_block_ratio=0.5, seg_len=64, use_graph=False, seed=seed)
+                       feature_block_ratio=0.5, seg_len=64, use_graph=graph, seed=seed, fused=fused)
     shards = [make_rcv1_like(n_rows, n_feat, 24.0, seed=seed, shard=r, device=dev, binary=binary)
               for r in range(world)]
 
@@ -61,7 +62,11 @@ def _run_compare(world, binary, tau, passes=4, n_rows=3000, n_feat=700, lam=0.5,
     for it in range(passes):
         order = list(range(len(blocks)))
         rng.shuffle(order)
-        p = run_pass_lockstep(engines, order, thr, reset)
+        if fused:
+            assert world == 1
+            p = e0.run_pass(order, thr, reset)
+        else:
+            p = run_pass_lockstep(engines, order, thr, reset)
         ref = run_oracle_pass(workers, server, blocks, order, thr, reset, e0.bps)
         assert p.nnz_w == ref["nnz_w"], (it, p.nnz_w, ref["nnz_w"])
         assert p.nnz_active_set == ref["nnz_active"], (it, p.nnz_active_set, ref["nnz_active"])
@@ -76,7 +81,8 @@ def _run_compare(world, binary, tau, passes=4, n_rows=3000, n_feat=700, lam=0.5,
     assert torch.equal(torch.isnan(w_dev), torch.isnan(server.w))
     assert torch.allclose(torch.where(both_nan, 0, w_dev), torch.where(both_nan, 0, server.w),
                           rtol=1e-9, atol=1e-12)
-    assert int(torch.isnan(server.w).sum()) > 0, "test should exercise the KKT filter"
+    if expect_filter:
+        assert int(torch.isnan(server.w).sum()) > 0, "test should exercise the KKT filter"
     for e in engines:
         e.close()
 
@@ -99,6 +105,20 @@ def test_darlin_two_emulated_ranks():
 
 def test_darlin_three_emulated_ranks_delay_tail():
     _run_compare(world=3, binary=False, tau=1, tail=2)
+
+
+def test_darlin_fused_persistent_kernel_matches_oracle():
+    _run_compare(world=1, binary=False, tau=0, fused=True)
+
+
+def test_darlin_fused_binary_delay_graph():
+    _run_compare(world=1, binary=True, tau=3, lam=2.0, fused=True, graph=True)
+
+
+def test_darlin_fused_large_grid_many_segments():
+    # more segments than resident warps and long multi-segment columns
+    _run_compare(world=1, binary=False, tau=1, n_rows=60000, n_feat=300, fused=True,
+                 expect_filter=False)
 
 
 def test_darlin_graph_train_decreases_objective(tmp_path):
