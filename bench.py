@@ -92,6 +92,9 @@ def main() -> None:
     ap.add_argument("--block-ratio", type=float, default=4.0)
     ap.add_argument("--seg-len", type=int, default=256)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--profile-phases", action="store_true")
+    ap.add_argument("--kernel-flags", type=int, default=0)
+    ap.add_argument("--fused-grid", type=int, default=0)
     ap.add_argument("--split", action="store_true", help="3 kernels per step instead of the persistent pass kernel")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -120,7 +123,9 @@ def main() -> None:
 
     cfg = DarlinConfig(lambda_l1=1.0, eta=1.0, max_pass_of_data=args.steps + args.warmup,
                        epsilon=0.0, feature_block_ratio=args.block_ratio,
-                       max_block_delay=args.tau, seg_len=args.seg_len, use_graph=not args.no_graph, fused=not args.split)
+                       max_block_delay=args.tau, seg_len=args.seg_len, use_graph=not args.no_graph, fused=not args.split,
+                       profile_phases=args.profile_phases, kernel_flags=args.kernel_flags,
+                       fused_grid=args.fused_grid)
     t0 = time.time()
     data = make_rcv1_like(args.rows, args.features, args.nnz_per_row, seed=0, shard=rank, device=dev)
     eng = DarlinEngine(cfg, comm, dev, out=sys.stderr)
@@ -165,6 +170,18 @@ def main() -> None:
     t_wall = time.perf_counter() - t_wall0
     span_ms = ev0.elapsed_time(ev1)
     clocks = sampler.stop() if rank == 0 else None
+    if args.profile_phases and rank == 0:
+        pr = eng.prof.cpu().tolist()
+        passes = args.steps + args.warmup
+        nst = max(len(eng.blocks) // eng.bps, 1)
+        names = ['phase1', 'plan+prefetch', 'barrierA', 'phase3', 'barrierC']
+        import collections
+        mx = pr[8:8 + 2 * nst]
+        p1 = [v >> 20 for v in mx[0::2]]; p3 = [v >> 20 for v in mx[1::2]]
+        print('max-over-CTA phase1 us mean %.2f, phase3 %.2f (max over passes); straggler CTAs p1 %s p3 %s' % (sum(p1) / len(p1) / 1e3, sum(p3) / len(p3) / 1e3, collections.Counter(v & 0xfffff for v in mx[0::2]).most_common(4), collections.Counter(v & 0xfffff for v in mx[1::2]).most_common(4)), file=sys.stderr)
+        sp = sorted(p1); print('phase1 max-over-CTA quantiles us:', [round(sp[int(q * (len(sp) - 1))] / 1e3, 1) for q in (0, .1, .25, .5, .75, .9, .99, 1)], file=sys.stderr)
+        sp = sorted(p3); print('phase3 max-over-CTA quantiles us:', [round(sp[int(q * (len(sp) - 1))] / 1e3, 1) for q in (0, .1, .25, .5, .75, .9, .99, 1)], file=sys.stderr)
+        print('per-step us (mean over CTAs):', {n: round(v / eng.grid_fused / passes / nst / 1e3, 2) for n, v in zip(names, pr)}, file=sys.stderr)
 
     times = torch.tensor([dev_ms, span_ms, t_wall * 1e3, ker_ms], dtype=torch.float64, device=dev)
     if world > 1:

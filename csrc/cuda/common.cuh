@@ -95,9 +95,19 @@ __device__ __forceinline__ void grid_arrive(uint32_t* ctr) {
   __syncthreads();
   if (threadIdx.x == 0) red_release_gpu_add(ctr, 1u);
 }
+__device__ __forceinline__ uint32_t ld_relaxed_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+// poll relaxed (an acquire load invalidates L1 on every iteration), fence once at the end
+__device__ __forceinline__ void spin_gpu_ge(const uint32_t* ctr, uint32_t target) {
+  while (ld_relaxed_gpu(ctr) < target) {}
+  fence_acq_rel_gpu();
+}
 __device__ __forceinline__ void grid_wait(const uint32_t* ctr, uint32_t target) {
-  if (threadIdx.x == 0)
-    while (ld_acquire_gpu(ctr) < target) {}
+  if (threadIdx.x == 0) spin_gpu_ge(ctr, target);
   __syncthreads();
 }
 __device__ __forceinline__ void spin_until_ge(const uint64_t* flag, uint64_t want) {

@@ -488,15 +488,317 @@ __device__ __forceinline__ void fused_plan(FusedPlan& P, const int64_t* __restri
   if (lane == 0) { P.wk.mask = mask; P.sv.mask = mask; }
 }
 
+// ---- packed-metadata phases used by the persistent kernel -------------------------------------
+struct SegMeta {
+  int64_t j, beg;
+  int len;
+  bool first, single;
+};
+__device__ __forceinline__ SegMeta load_meta(const void* seg_meta, int64_t s) {
+  const int4 m = __ldg(reinterpret_cast<const int4*>(seg_meta) + s);
+  SegMeta r;
+  r.j = m.x;
+  r.len = m.y & 0xffff;
+  r.first = (m.y >> 16) & 1;
+  r.single = (m.y >> 17) & 1;
+  r.beg = (int64_t)(uint32_t)m.z | ((int64_t)m.w << 32);
+  return r;
+}
+
+__device__ __forceinline__ uint32_t atom_add_acqrel_gpu(uint32_t* p, uint32_t v) {
+  uint32_t old;
+  asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+constexpr int kUnroll = 4;  // 4 x 32 lanes = one 128-entry segment per batch
+
+// One coordinate of the server update with its state already in registers (ref
+// darlin.h:216-245).  Used by the single-rank persistent kernel, where the warp that finishes
+// a column's gradient applies the update at once: no landing slot, no second synchronisation.
+__device__ __forceinline__ double update_coord(const psb_darlin_server& S, const ServerHyper& h,
+                                               int64_t k, double g, double u, double w, double dl,
+                                               bool active) {
+  if (!active || is_marked(w)) return 0;
+  u = u / h.eta + 1e-10;
+  const double g_pos = g + h.lambda, g_neg = g - h.lambda;
+  double d = -w, vio = 0;
+  if (w == 0) {
+    if (g_pos < 0) {
+      vio = -g_pos;
+    } else if (g_neg > 0) {
+      vio = g_neg;
+    } else if (g_pos > h.thr && g_neg < -h.thr) {
+      bit_clear_atomic(S.active, k);
+      S.w[k] = nan_mark();
+      S.dw[k] = 0;
+      return 0;
+    }
+  }
+  if (g_pos <= u * w) {
+    d = -g_pos / u;
+  } else if (g_neg >= u * w) {
+    d = -g_neg / u;
+  }
+  d = fmin(dl, fmax(-dl, d));
+  S.delta[k] = fmin(h.delta_max, 2 * fabs(d) + .1);
+  const double w_new = w + d;
+  S.w[k] = w_new;
+  S.dw[k] = w_new - w;
+  return vio;
+}
+
+template <bool BINARY, bool SINGLE>
+__device__ __forceinline__ double grad_phase_packed(const psb_darlin_worker& W, const psb_darlin_server& S,
+                                                    const ServerHyper& h, const StepPlan& plan,
+                                                    int bps, int64_t gw, int64_t nw, int lane) {
+  const int64_t total = plan.pref[bps];
+  double vio_max = 0;
+  for (int64_t v = gw; v < total; v += nw) {
+    const int q = locate(plan, bps, v);
+    const int64_t s = plan.first[q] + (v - plan.pref[q]);
+    const SegMeta m = load_meta(W.seg_meta, s);
+    // one latency level: active word, delta and the first batch of indices/values together
+    const uint32_t aw = __ldcg(W.active + (m.j >> 5));
+    double d = __ldcg(W.delta + m.j);
+    int64_t sk = 0;          // shard coordinate (single-rank: this GPU owns every column)
+    double sw = 0, sdl = 0;  // its weight and trust region, fetched off the critical path
+    uint32_t saw = 0;
+    if (SINGLE) sk = __ldg(W.col_off + m.j);
+    double g = 0, u = 0;
+    for (int base = 0; base < m.len; base += 32 * kUnroll) {
+      uint32_t idx[kUnroll];
+      float sv[kUnroll];
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k) {
+        const int e = base + k * 32 + lane;
+        const bool ok = e < m.len;
+        idx[k] = ok ? __ldg(W.row_idx + m.beg + e) : 0xffffffffu;
+        sv[k] = (ok && !BINARY) ? __ldg(W.sval + m.beg + e) : 0.f;
+      }
+      if (!(aw >> (m.j & 31) & 1u)) break;  // inactive column: nothing is pushed
+      if (base == 0 && BINARY) d = exp(d);
+      if (SINGLE && base == 0 && lane == 0) {
+        sw = __ldcg(S.w + sk);
+        sdl = __ldcg(S.delta + sk);
+        saw = __ldcg(S.active + (sk >> 5));
+      }
+      double zz[kUnroll];
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k) {
+        zz[k] = idx[k] != 0xffffffffu ? __ldcg(W.z + idx[k]) : 0.0;
+        if (BINARY) sv[k] = idx[k] != 0xffffffffu ? __ldg(W.y + idx[k]) : 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k) {
+        if (idx[k] == 0xffffffffu) continue;
+        const double tau = 1.0 / (1.0 + exp(zz[k]));
+        const double x = (double)sv[k];
+        if (BINARY) {
+          g -= x * tau;
+          u += fmin(tau * (1.0 - tau) * d, 0.25);
+        } else {
+          g -= tau * x;
+          u += fmin(tau * (1.0 - tau) * exp(fabs(x) * d), 0.25) * x * x;
+        }
+      }
+    }
+    if (!(aw >> (m.j & 31) & 1u)) continue;
+    g = warp_sum(g);
+    u = warp_sum(u);
+    if (m.single) {
+      if (lane == 0) {
+        if (SINGLE) vio_max = fmax(vio_max, update_coord(S, h, sk, g, u, sw, sdl, saw >> (sk & 31) & 1u));
+        else push_column(W, m.j, g, u);
+      }
+      continue;
+    }
+    const int64_t cs = W.col_seg[m.j];
+    const int nseg = (int)(W.col_seg[m.j + 1] - cs);
+    int old = 0;
+    if (lane == 0) {
+      __stcg(W.part + 2 * v, g);
+      __stcg(W.part + 2 * v + 1, u);
+      // release: the partial is visible before the count; acquire: the last arriver sees all
+      old = (int)atom_add_acqrel_gpu(reinterpret_cast<uint32_t*>(W.col_cnt + m.j), 1u);
+    }
+    old = __shfl_sync(FULL, old, 0);
+    if (old == nseg - 1) {
+      const int64_t v0 = v - (s - cs);
+      double sg = 0, su = 0;
+      for (int k = lane; k < nseg; k += 32) {
+        sg += __ldcg(W.part + 2 * (v0 + k));
+        su += __ldcg(W.part + 2 * (v0 + k) + 1);
+      }
+      sg = warp_sum(sg);
+      su = warp_sum(su);
+      if (lane == 0) {
+        if (SINGLE) vio_max = fmax(vio_max, update_coord(S, h, sk, sg, su, sw, sdl, saw >> (sk & 31) & 1u));
+        else push_column(W, m.j, sg, su);
+        W.col_cnt[m.j] = 0;
+      }
+    }
+  }
+  return vio_max;
+}
+
 template <bool BINARY>
+__device__ __forceinline__ void pull_phase_packed(const psb_darlin_worker& W, const StepPlan& plan,
+                                                  int bps, double delta_max, int64_t gw, int64_t nw,
+                                                  int lane) {
+  const int64_t total = plan.pref[bps];
+  for (int64_t v = gw; v < total; v += nw) {
+    const int q = locate(plan, bps, v);
+    const int64_t s = plan.first[q] + (v - plan.pref[q]);
+    const SegMeta m = load_meta(W.seg_meta, s);
+    const int o = __ldg(W.col_owner + m.j);
+    const int64_t off = __ldg(W.col_off + m.j);
+    const uint32_t aw = __ldcg(W.active + (m.j >> 5));
+    double w_new = 0, d = 0;
+    if (lane == 0) {
+      w_new = ld_volatile_f64(W.srv_w[o] + off);  // peer load when o != rank
+      d = ld_volatile_f64(W.srv_dw[o] + off);
+    }
+    uint32_t idx[kUnroll];
+    float sv[kUnroll];
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) {  // speculative first batch, overlaps the w/dw round trip
+      const int e = k * 32 + lane;
+      const bool ok = e < m.len;
+      idx[k] = ok ? __ldg(W.row_idx + m.beg + e) : 0xffffffffu;
+      sv[k] = (ok && !BINARY) ? __ldg(W.sval + m.beg + e) : 0.f;
+    }
+    w_new = __shfl_sync(FULL, w_new, 0);
+    d = __shfl_sync(FULL, d, 0);
+    if (is_marked(w_new)) {  // the server filtered this coordinate (ref darlin.h:439-444)
+      if (m.first && lane == 0) {
+        bit_clear_atomic(W.active, m.j);
+        W.w[m.j] = 0;
+      }
+      continue;
+    }
+    if (!(aw >> (m.j & 31) & 1u)) continue;
+    if (m.first && lane == 0) {
+      W.w[m.j] = w_new;
+      W.delta[m.j] = fmin(delta_max, 2 * fabs(d) + .1);
+    }
+    if (d == 0) continue;
+    for (int base = 0; base < m.len; base += 32 * kUnroll) {
+      if (base > 0) {
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k) {
+          const int e = base + k * 32 + lane;
+          const bool ok = e < m.len;
+          idx[k] = ok ? __ldg(W.row_idx + m.beg + e) : 0xffffffffu;
+          sv[k] = (ok && !BINARY) ? __ldg(W.sval + m.beg + e) : 0.f;
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k) {
+        if (idx[k] == 0xffffffffu) continue;
+        const double x = BINARY ? (double)__ldg(W.y + idx[k]) : (double)sv[k];
+        atomicAdd(W.z + idx[k], d * x);  // dual_i *= exp(y_i d x_ij)  <=>  z_i += d * sval
+      }
+    }
+  }
+}
+
+// same update as server_phase, with every load of a coordinate issued before any use
+__device__ __forceinline__ double server_phase_ilp(const psb_darlin_server& S, const ServerHyper& h,
+                                                   const StepPlan& plan, int bps, int64_t tid,
+                                                   int64_t nthreads) {
+  const int64_t total = plan.pref[bps];
+  double vio_max = 0;
+  for (int64_t v = tid; v < total; v += nthreads) {
+    const int q = locate(plan, bps, v);
+    const int64_t k = plan.first[q] + (v - plan.pref[q]);
+    const uint32_t aw = __ldcg(S.active + (k >> 5));
+    const double w = __ldcg(S.w + k);
+    const double dl = __ldcg(S.delta + k);
+    double g = 0, u = 0;
+    for (int r = 0; r < S.n_workers; ++r) {
+      const int64_t at = (int64_t)r * S.land_cap + k;
+      g += __ldcg(S.land_g + at);
+      u += __ldcg(S.land_u + at);
+    }
+    if (!(aw >> (k & 31) & 1u) || is_marked(w)) continue;
+    u = u / h.eta + 1e-10;
+    const double g_pos = g + h.lambda, g_neg = g - h.lambda;
+    double d = -w, vio = 0;
+    if (w == 0) {
+      if (g_pos < 0) {
+        vio = -g_pos;
+      } else if (g_neg > 0) {
+        vio = g_neg;
+      } else if (g_pos > h.thr && g_neg < -h.thr) {
+        bit_clear_atomic(S.active, k);
+        S.w[k] = nan_mark();
+        S.dw[k] = 0;
+        continue;
+      }
+    }
+    vio_max = fmax(vio_max, vio);
+    if (g_pos <= u * w) {
+      d = -g_pos / u;
+    } else if (g_neg >= u * w) {
+      d = -g_neg / u;
+    }
+    d = fmin(dl, fmax(-dl, d));
+    S.delta[k] = fmin(h.delta_max, 2 * fabs(d) + .1);
+    const double w_new = w + d;
+    S.w[k] = w_new;
+    S.dw[k] = w_new - w;
+  }
+  return vio_max;
+}
+
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+// warm L2 with the CSC ranges this CTA's warps will read in the next step
+template <bool BINARY>
+__device__ __forceinline__ void prefetch_step(const psb_darlin_worker& W, const StepPlan& plan, int bps,
+                                              int64_t gw, int64_t nw, int lane) {
+  const int64_t total = plan.pref[bps];
+  for (int64_t v = gw; v < total; v += nw) {
+    const int q = locate(plan, bps, v);
+    const int64_t s = plan.first[q] + (v - plan.pref[q]);
+    const SegMeta m = load_meta(W.seg_meta, s);
+    const int lines = (m.len * 4 + 127) / 128 + 1;
+    if (lane < lines) prefetch_l2(reinterpret_cast<const char*>(W.row_idx + m.beg) + lane * 128);
+    if (!BINARY && lane >= 16 && lane - 16 < lines)
+      prefetch_l2(reinterpret_cast<const char*>(W.sval + m.beg) + (lane - 16) * 128);
+  }
+}
+
+
+// bar[0] phase-1 arrivals, bar[1] "server done" step stamp, bar[2] phase-3 arrivals,
+// bar[3] generic barrier (begin / large steps / evaluate).  All zero between launches.
+constexpr int64_t kSingleCtaServerKeys = 16 * kThreads;
+
+template <bool BINARY, bool SINGLE>
 __global__ void __launch_bounds__(kThreads, 2)
 k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant__ psb_darlin_server S,
               const psb_darlin_ctrl* __restrict__ ctrl, const int32_t* __restrict__ order,
               const int64_t* __restrict__ blk_tab, int n_steps, int bps, uint32_t* bar,
               psb_darlin_progress* out_local, psb_darlin_progress* const* out_peer, int n_peers,
-              double* scratch) {
+              double* scratch, unsigned long long* prof) {
   __shared__ FusedPlan plans[2];
   __shared__ double sh[4][kWarps];
+  __shared__ bool s_last;
+  // optional per-phase time accounting (thread 0 of every CTA, summed into prof[0..4])
+  unsigned long long t_mark = 0, t_acc[5] = {0, 0, 0, 0, 0};
+#define PSB_PROF(slot)                                         \
+  if (prof && threadIdx.x == 0) {                              \
+    unsigned long long now_;                                   \
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));   \
+    t_acc[slot] += now_ - t_mark;                              \
+    t_mark = now_;                                             \
+  }
+  if (prof && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_mark));
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int64_t gw = (int64_t)blockIdx.x * kWarps + wid, nw = (int64_t)gridDim.x * kWarps;
   const int64_t gt = (int64_t)blockIdx.x * kThreads + threadIdx.x, nt = (int64_t)gridDim.x * kThreads;
@@ -505,6 +807,8 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
   const bool multi = W.n_workers > 1;
   const ServerHyper h{ctrl->lambda, ctrl->eta, ctrl->delta_max, ctrl->kkt_threshold};
   const uint64_t seq_base = ctrl->seq_base;
+  const bool do_prefetch = !(ctrl->flags & 1);
+  const int64_t single_cta_keys = ctrl->server_cta_keys > 0 ? ctrl->server_cta_keys : kSingleCtaServerKeys;
 
   // ---- pass begin (ref darlin.h:176-182, 297-300) ----
   if (gt == 0) *S.violation = 0;
@@ -522,42 +826,107 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
         if (is_marked(__ldcg(S.w + i))) S.w[i] = 0;
   }
   if (wid == 0 && n_steps > 0) fused_plan(plans[0], blk_tab, order, 0, bps);
-  grid_arrive(bar);
-  grid_wait(bar, ++nbar * G);
+  grid_arrive(bar + 3);
+  grid_wait(bar + 3, ++nbar * G);
 
   for (int step = 0; step < n_steps; ++step) {
     const FusedPlan& P = plans[step & 1];
+    const FusedPlan& Pn = plans[(step + 1) & 1];
     const uint64_t seq = seq_base + (uint64_t)step + 1;
-    // ---- phase 1: gradient + push ----
-    grad_phase<BINARY>(W, P.wk, bps, gw, nw, lane);
-    grid_arrive(bar);
-    if (wid == 0 && step + 1 < n_steps) fused_plan(plans[(step + 1) & 1], blk_tab, order, step + 1, bps);
-    grid_wait(bar, ++nbar * G);
-    if (multi && blockIdx.x == G - 1 && threadIdx.x < W.n_servers && threadIdx.x != W.rank &&
-        (P.wk.mask >> threadIdx.x & 1u)) {
-      __threadfence_system();
-      st_release_sys(W.push_flag[threadIdx.x] + W.rank, seq);
-    }
-    // ---- phase 2: server update on the first CTAs ----
     const int64_t nkeys = P.sv.pref[bps];
-    double vio = 0;
-    if (nkeys > 0 && (int64_t)blockIdx.x * kThreads < nkeys) {
+    const bool has_next = step + 1 < n_steps;
+    // ---- phase 1: gradient + push ----
+    {
+      const int64_t gwr = (ctrl->flags & 2) ? (gw + (int64_t)step * 8 * 37) % nw : gw;  // experiment
+      const double vio = grad_phase_packed<BINARY, SINGLE>(W, S, h, P.wk, bps, gwr, nw, lane);
+      if (SINGLE && vio > 0) atomic_max_nonneg(S.violation, vio);
+    }
+    if (prof && threadIdx.x == 0) {  // per-step straggler: max phase-1 time and its CTA
+      unsigned long long now_;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
+      atomicMax(prof + 8 + 2 * step, ((now_ - t_mark) << 20) | blockIdx.x);
+    }
+    PSB_PROF(0)
+    if (SINGLE) {
+      // one rank: the shard was updated column by column inside phase 1; a single grid
+      // barrier separates the margin reads of phase 1 from the margin updates of phase 3
+      grid_arrive(bar);
+      if (wid == 0 && has_next) fused_plan(plans[(step + 1) & 1], blk_tab, order, step + 1, bps);
+      __syncthreads();
+      if (has_next && do_prefetch) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
+      PSB_PROF(1)
+      grid_wait(bar, (uint32_t)(step + 1) * G);
+      PSB_PROF(2)
+      pull_phase_packed<BINARY>(W, P.wk, bps, h.delta_max, gw, nw, lane);
+      if (prof && threadIdx.x == 0) {
+        unsigned long long now_;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
+        atomicMax(prof + 9 + 2 * step, ((now_ - t_mark) << 20) | blockIdx.x);
+      }
+      PSB_PROF(3)
+      grid_arrive(bar + 2);
+      grid_wait(bar + 2, (uint32_t)(step + 1) * G);
+      PSB_PROF(4)
+      continue;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+      s_last = atom_add_acqrel_gpu(bar, 1u) == (uint32_t)(step + 1) * G - 1u;
+    if (wid == 0 && has_next) fused_plan(plans[(step + 1) & 1], blk_tab, order, step + 1, bps);
+    __syncthreads();
+    if (nkeys <= single_cta_keys) {
+      // ---- phase 2, small step: the CTA that finished phase 1 last updates the shard at once,
+      //      everybody else warms L2 for the next step and waits for its stamp ----
+      if (s_last) {
+        if (multi) {
+          if (threadIdx.x < W.n_servers && threadIdx.x != W.rank && (P.wk.mask >> threadIdx.x & 1u)) {
+            __threadfence_system();
+            st_release_sys(W.push_flag[threadIdx.x] + W.rank, seq);
+          }
+          if (nkeys > 0 && threadIdx.x < S.n_workers && threadIdx.x != S.rank)
+            spin_until_ge(S.push_flag + threadIdx.x, seq);
+          __syncthreads();
+        }
+        if (nkeys > 0) {
+          double vio = server_phase_ilp(S, h, P.sv, bps, threadIdx.x, kThreads);
+          vio = warp_max(vio);
+          if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
+          __syncthreads();
+          if (multi && threadIdx.x < S.n_workers && threadIdx.x != S.rank) {
+            __threadfence_system();
+            st_release_sys(S.ver_flag[threadIdx.x], seq);
+          }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) st_release_gpu(bar + 1, (uint32_t)(step + 1));
+      } else {
+        if (has_next && do_prefetch) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
+        if (threadIdx.x == 0) spin_gpu_ge(bar + 1, (uint32_t)(step + 1));
+      }
+      __syncthreads();
+    } else {
+      // ---- phase 2, large step: all CTAs share the coordinates between two grid barriers ----
+      grid_wait(bar, (uint32_t)(step + 1) * G);
+      if (multi && blockIdx.x == G - 1 && threadIdx.x < W.n_servers && threadIdx.x != W.rank &&
+          (P.wk.mask >> threadIdx.x & 1u)) {
+        __threadfence_system();
+        st_release_sys(W.push_flag[threadIdx.x] + W.rank, seq);
+      }
       if (multi) {
         if (threadIdx.x < S.n_workers && threadIdx.x != S.rank)
           spin_until_ge(S.push_flag + threadIdx.x, seq);
         __syncthreads();
       }
-      const int64_t ncta = min((int64_t)G, (nkeys + kThreads - 1) / kThreads);
-      vio = server_phase(S, h, P.sv, bps, gt, ncta * kThreads);
+      double vio = server_phase_ilp(S, h, P.sv, bps, gt, nt);
       vio = warp_max(vio);
       if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
-    }
-    grid_arrive(bar);
-    grid_wait(bar, ++nbar * G);
-    if (multi && nkeys > 0 && blockIdx.x == G - 1 && threadIdx.x < S.n_workers &&
-        threadIdx.x != S.rank) {
-      __threadfence_system();
-      st_release_sys(S.ver_flag[threadIdx.x], seq);
+      grid_arrive(bar + 3);
+      grid_wait(bar + 3, ++nbar * G);
+      if (multi && blockIdx.x == G - 1 && threadIdx.x < S.n_workers && threadIdx.x != S.rank) {
+        __threadfence_system();
+        st_release_sys(S.ver_flag[threadIdx.x], seq);
+      }
+      if (threadIdx.x == 0 && blockIdx.x == 0) st_release_gpu(bar + 1, (uint32_t)(step + 1));
     }
     // ---- phase 3: pull + margin update ----
     if (multi && P.wk.pref[bps] > 0) {
@@ -565,10 +934,16 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
         spin_until_ge(W.ver_flag + threadIdx.x, seq);
       __syncthreads();
     }
-    pull_phase<BINARY>(W, P.wk, bps, h.delta_max, gw, nw, lane);
-    grid_arrive(bar);
-    grid_wait(bar, ++nbar * G);
+    PSB_PROF(2)
+    pull_phase_packed<BINARY>(W, P.wk, bps, h.delta_max, gw, nw, lane);
+    PSB_PROF(3)
+    grid_arrive(bar + 2);
+    grid_wait(bar + 2, (uint32_t)(step + 1) * G);
+    PSB_PROF(4)
   }
+  if (prof && threadIdx.x == 0)
+    for (int i = 0; i < 5; ++i) atomicAdd(prof + i, t_acc[i]);
+#undef PSB_PROF
 
   // ---- evaluate (ref darlin.h:248-265, 504-511) ----
   double loss = 0, l1 = 0, dn = 0, da = 0;
@@ -589,9 +964,9 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
     for (int i = 0; i < kWarps; ++i) a += sh[threadIdx.x][i];
     __stcg(scratch + 4 * (int64_t)blockIdx.x + threadIdx.x, a);
   }
-  grid_arrive(bar);
+  grid_arrive(bar + 3);
   if (blockIdx.x != 0) return;
-  grid_wait(bar, ++nbar * G);
+  grid_wait(bar + 3, ++nbar * G);
   double acc[4] = {0, 0, 0, 0};
   for (int b = threadIdx.x; b < (int)G; b += kThreads)
     for (int c = 0; c < 4; ++c) acc[c] += __ldcg(scratch + 4 * (int64_t)b + c);
@@ -605,7 +980,8 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
       for (int i = 0; i < kWarps; ++i) a += sh[c][i];
       acc[c] = a;
     }
-    *bar = 0;  // every CTA has arrived at the last barrier; nobody reads the counter again
+    // every CTA has arrived at the last barrier; nobody reads the counters again
+    bar[0] = 0; bar[1] = 0; bar[2] = 0; bar[3] = 0;
     const double vio = __ldcg(S.violation);
     const uint64_t stamp = seq_base + (uint64_t)n_steps;
     for (int r = -1; r < n_peers; ++r) {
@@ -723,8 +1099,8 @@ PSB_API int psb_darlin_enqueue_pass(const psb_darlin_worker* wk, const psb_darli
 PSB_API int psb_darlin_fused_max_grid(int32_t binary) {
   int per_sm = 0;
   cudaError_t e = binary
-      ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_darlin_pass<true>, kThreads, 0)
-      : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_darlin_pass<false>, kThreads, 0);
+      ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_darlin_pass<true, false>, kThreads, 0)
+      : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_darlin_pass<false, false>, kThreads, 0);
   if (e != cudaSuccess || per_sm < 1) return 0;
   return per_sm * sm_count();
 }
@@ -734,7 +1110,7 @@ PSB_API int psb_darlin_fused_pass(const psb_darlin_worker* wk, const psb_darlin_
                                   const int64_t* blk_tab, int32_t n_steps, int32_t bps,
                                   int32_t grid, uint32_t* bar, psb_darlin_progress* out_local,
                                   psb_darlin_progress* const* out_peer, int32_t n_peers,
-                                  double* scratch, void* stream) {
+                                  double* scratch, uint64_t* prof, void* stream) {
   PSB_REQUIRE(wk && sv && ctrl && order && blk_tab && bar && scratch, "psb_darlin_fused_pass: NULL argument");
   if (int rc = check_step_args("psb_darlin_fused_pass", bps, grid)) return rc;
   PSB_REQUIRE(grid <= psb_darlin_fused_max_grid(wk->sval == nullptr),
@@ -742,8 +1118,11 @@ PSB_API int psb_darlin_fused_pass(const psb_darlin_worker* wk, const psb_darlin_
   int np = out_peer ? n_peers : 0;
   void* args[] = {(void*)wk, (void*)sv, (void*)&ctrl, (void*)&order, (void*)&blk_tab, (void*)&n_steps,
                   (void*)&bps, (void*)&bar, (void*)&out_local, (void*)&out_peer, (void*)&np,
-                  (void*)&scratch};
-  const void* fn = wk->sval ? (const void*)k_darlin_pass<false> : (const void*)k_darlin_pass<true>;
+                  (void*)&scratch, (void*)&prof};
+  const bool single = wk->n_workers == 1 && wk->n_servers == 1;
+  const void* fn = wk->sval
+      ? (single ? (const void*)k_darlin_pass<false, true> : (const void*)k_darlin_pass<false, false>)
+      : (single ? (const void*)k_darlin_pass<true, true> : (const void*)k_darlin_pass<true, false>);
   PSB_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), args, 0, (cudaStream_t)stream));
   return 0;
 }

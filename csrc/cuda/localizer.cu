@@ -130,13 +130,20 @@ __global__ void k_seg_count(const int64_t* __restrict__ col_ptr, int64_t n_cols,
 
 __global__ void k_seg_fill(const int64_t* __restrict__ col_ptr, const int64_t* __restrict__ col_seg,
                            int64_t n_cols, int seg_len, int32_t* __restrict__ seg_col,
-                           int64_t* __restrict__ seg_beg) {
+                           int64_t* __restrict__ seg_beg, int4* __restrict__ seg_meta) {
   for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < n_cols;
        c += (int64_t)gridDim.x * blockDim.x) {
     const int64_t s0 = col_seg[c], s1 = col_seg[c + 1];
     for (int64_t s = s0; s < s1; ++s) {
+      const int64_t beg = col_ptr[c] + (s - s0) * seg_len;
       seg_col[s] = (int32_t)c;
-      seg_beg[s] = col_ptr[c] + (s - s0) * seg_len;
+      seg_beg[s] = beg;
+      if (seg_meta) {  // {col, len | first<<16 | single<<17, beg lo, beg hi}
+        int64_t len = col_ptr[c + 1] - beg;
+        len = len < 0 ? 0 : (len > seg_len ? seg_len : len);
+        const int flags = (int)len | ((s == s0) << 16) | ((s1 - s0 == 1) << 17);
+        seg_meta[s] = make_int4((int)c, flags, (int)(uint32_t)(beg & 0xffffffffLL), (int)(beg >> 32));
+      }
     }
   }
 }
@@ -312,10 +319,12 @@ PSB_API int psb_segments_count(const int64_t* col_ptr, int64_t n_cols, int32_t s
   return psb_exclusive_sum_i64(col_seg, col_seg, n_cols + 1, temp, temp_bytes, stream);
 }
 PSB_API int psb_segments_fill(const int64_t* col_ptr, const int64_t* col_seg, int64_t n_cols,
-                              int32_t seg_len, int32_t* seg_col, int64_t* seg_beg, void* stream) {
+                              int32_t seg_len, int32_t* seg_col, int64_t* seg_beg,
+                              void* seg_meta, void* stream) {
+  PSB_REQUIRE(seg_len <= 32768, "psb_segments_fill: seg_len must be <= 32768");
   if (n_cols == 0) return 0;
   k_seg_fill<<<grid_for(n_cols), 256, 0, (cudaStream_t)stream>>>(col_ptr, col_seg, n_cols, seg_len,
-                                                                 seg_col, seg_beg);
+                                                                 seg_col, seg_beg, (int4*)seg_meta);
   PSB_LAUNCH_CHECK();
   return 0;
 }

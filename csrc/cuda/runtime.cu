@@ -147,3 +147,35 @@ PSB_API int psb_rank_barrier_dev(uint64_t* const* peers_host, int rank, int worl
   PSB_LAUNCH_CHECK();
   return 0;
 }
+
+// ---- micro-benchmarks (used by profiles/ and tests; not on any product path) ------------------
+namespace psb {
+__global__ void __launch_bounds__(256, 2) k_bench_grid_barrier(uint32_t* bar, int iters, int mode) {
+  const uint32_t G = gridDim.x;
+  for (int i = 0; i < iters; ++i) {
+    if (mode == 0) {  // split arrive/wait, relaxed polling (what k_darlin_pass uses)
+      grid_arrive(bar);
+      grid_wait(bar, (uint32_t)(i + 1) * G);
+    } else {          // acquire polling
+      grid_arrive(bar);
+      if (threadIdx.x == 0)
+        while (ld_acquire_gpu(bar) < (uint32_t)(i + 1) * G) {}
+      __syncthreads();
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    // all CTAs passed the last wait only after everybody arrived; safe to clear for the next launch
+  }
+}
+__global__ void k_clear_u32(uint32_t* p) { *p = 0; }
+}  // namespace psb
+
+// time per grid barrier: launch cooperative kernel with `iters` barriers; caller times it.
+PSB_API int psb_bench_grid_barrier(uint32_t* bar, int32_t iters, int32_t grid, int32_t mode,
+                                   void* stream) {
+  psb::k_clear_u32<<<1, 1, 0, (cudaStream_t)stream>>>(bar);
+  void* args[] = {(void*)&bar, (void*)&iters, (void*)&mode};
+  PSB_CUDA(cudaLaunchCooperativeKernel((const void*)psb::k_bench_grid_barrier, dim3(grid), dim3(256),
+                                       args, 0, (cudaStream_t)stream));
+  return 0;
+}

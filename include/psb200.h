@@ -41,6 +41,9 @@ typedef struct psb_darlin_ctrl {
   int32_t n_steps;           /* steps in this pass */
   int32_t revive_on_reset;   /* 1: a reset also un-marks filtered weights (w=NaN -> 0); the
                                 reference leaves them NaN forever, default 0 */
+  int32_t server_cta_keys;   /* persistent kernel: steps with at most this many shard keys are
+                                updated by one CTA (0 = default 4096); larger ones by the grid */
+  int32_t flags;             /* bit 0: do not prefetch the next step's CSC ranges into L2 */
   int32_t reserved;
 } psb_darlin_ctrl;
 
@@ -85,6 +88,8 @@ typedef struct psb_darlin_worker {
   const double* srv_w[PSB_MAX_PEERS]; /* server shard weights (NaN-marked when inactive) */
   const double* srv_dw[PSB_MAX_PEERS];/* server shard last step delta-w */
   const uint64_t* ver_flag;           /* local: [n_servers], written by the servers */
+  const void* seg_meta;               /* [n_seg] int4 {col, len | first<<16 | single<<17, beg lo,
+                                         beg hi}: one 16-byte load per segment (fused kernel) */
 } psb_darlin_worker;
 
 /* Server side: one key-range shard of the model. */
@@ -149,6 +154,20 @@ int psb_darlin_enqueue_pass(const psb_darlin_worker* wk, const psb_darlin_server
                             int32_t grid_server, psb_darlin_progress* out_local,
                             psb_darlin_progress* const* out_peer, int32_t n_peers,
                             double* eval_scratch, int32_t grid_eval, void* stream);
+
+/* Whole pass in ONE cooperative launch: pass_begin, every step and the evaluation run inside
+ * a persistent kernel whose phases are separated by grid barriers; with one rank the shard
+ * update is applied by the warp that completes a column's gradient.  `bar`: 4 zeroed uint32
+ * owned by the caller.  blk_tab[b] = {first segment, #segments, first shard key, #shard keys,
+ * server mask, 0}.  grid <= psb_darlin_fused_max_grid().  prof (optional): 5 uint64 that
+ * accumulate ns spent in {phase 1, plan+prefetch, barrier A wait, phase 3, barrier C}. */
+int psb_darlin_fused_max_grid(int32_t binary);
+int psb_darlin_fused_pass(const psb_darlin_worker* wk, const psb_darlin_server* sv,
+                          const psb_darlin_ctrl* ctrl, const int32_t* order,
+                          const int64_t* blk_tab, int32_t n_steps, int32_t blocks_per_step,
+                          int32_t grid, uint32_t* bar, psb_darlin_progress* out_local,
+                          psb_darlin_progress* const* out_peer, int32_t n_peers, double* scratch,
+                          uint64_t* prof, void* stream);
 
 #ifdef __cplusplus
 }

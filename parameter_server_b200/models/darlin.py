@@ -49,13 +49,17 @@ class DarlinConfig:
     delta_max_value: float = 5.0
     kkt_filter_threshold_ratio: float = 10.0
     # B200-specific knobs (no counterpart in the reference)
-    seg_len: int = 256                # nnz per warp work segment
+    seg_len: int = 128                # nnz per warp work segment
     shard_by: str = "data_range"      # "data_range": even split of [min_key,max_key);
     #                                   "all": Range::all() like postmaster.cc:17-31
     revive_on_reset: bool = False
     seed: int = 0
     use_graph: bool = True
     fused: bool = True                # one persistent cooperative kernel per pass
+    server_cta_keys: int = 0          # 0 = kernel default (see psb_darlin_ctrl)
+    kernel_flags: int = 0             # psb_darlin_ctrl.flags
+    fused_grid: int = 0               # 0 = all co-resident CTAs
+    profile_phases: bool = False      # accumulate per-phase %globaltimer time (debug)
 
     @staticmethod
     def from_proto(conf) -> "DarlinConfig":
@@ -177,7 +181,7 @@ class DarlinEngine:
         self.row_idx = torch.cat(ris).contiguous()
         self.sval = torch.cat(svs).contiguous() if not binary else None
         self.nnz = nnz_off
-        self.col_seg, self.seg_col, self.seg_beg = L.build_segments(self.col_ptr, cfg.seg_len)
+        self.col_seg, self.seg_col, self.seg_beg, self.seg_meta = L.build_segments(self.col_ptr, cfg.seg_len)
 
         self._divide_blocks(info)
         self._partition_servers()
@@ -322,7 +326,10 @@ class DarlinEngine:
         self.grid_server = int(max(1, min(math.ceil(self.bps * self.max_blk_keys / 256), sm)))
         self.grid_eval = int(sm * 2)
         self.grid_fused = K.fused_max_grid(self.sval is None) if cfg.fused else 0
+        if cfg.fused_grid > 0:
+            self.grid_fused = min(self.grid_fused, cfg.fused_grid)
         self.bar = torch.zeros(4, dtype=torch.int32, device=dev)
+        self.prof = torch.zeros(8 + 2 * (len(self.blocks) + len(self.prior_blk_order) + 2), dtype=torch.int64, device=dev)
         self.eval_scratch = torch.zeros(
             K.evaluate_scratch_bytes(max(self.grid_eval, 4 * sm)) // 8 + 2, **f64)
         # host-pinned staging for the per-pass inputs / result
@@ -355,6 +362,7 @@ class DarlinEngine:
             wk.srv_w[s] = A.peer_ptr(s, self.b_w)
             wk.srv_dw[s] = A.peer_ptr(s, self.b_dw)
         wk.ver_flag = self.b_ver_flag.ptr
+        wk.seg_meta = self.seg_meta.data_ptr()
         self.wk = wk
 
         sv = K.DarlinServer()
@@ -377,7 +385,7 @@ class DarlinEngine:
     def _warm_kernels(self) -> None:
         """Load every kernel once with an empty step so that graph capture never triggers a
         lazy module load; an all -1 order touches no state besides violation/progress."""
-        ctrl = K.DarlinCtrl(1e20, self.cfg.lambda_l1, self.cfg.eta, self.cfg.delta_max_value, 0, 0, 0, 0, 0)
+        ctrl = K.DarlinCtrl(1e20, self.cfg.lambda_l1, self.cfg.eta, self.cfg.delta_max_value, 0, 0, 0, 0, 0, 0, 0)
         self.ctrl_dev.copy_(torch.frombuffer(bytearray(bytes(ctrl)), dtype=torch.uint8))
         cp, op = self.ctrl_dev.data_ptr(), self.order_dev.data_ptr()
         K.pass_begin(self.wk, self.sv, cp)
@@ -396,7 +404,8 @@ class DarlinEngine:
                          self.blk_tab.data_ptr(), n_steps, self.bps, self.grid_fused,
                          self.bar.data_ptr(),
                          self.arena.peer_ptr(self.rank, self.b_progress, 6 * self.rank),
-                         self.prog_peer.data_ptr(), self.world, self.eval_scratch.data_ptr())
+                         self.prog_peer.data_ptr(), self.world, self.eval_scratch.data_ptr(),
+                         self.prof.data_ptr() if self.cfg.profile_phases else None)
         else:
             self._enqueue_split(n_steps)
         if self.world > 1:
@@ -430,7 +439,8 @@ class DarlinEngine:
             flat[i * self.bps:i * self.bps + len(st)] = st
         self.order_host[:flat.size] = torch.from_numpy(flat)
         ctrl = K.DarlinCtrl(kkt_threshold, cfg.lambda_l1, cfg.eta, cfg.delta_max_value, self._seq,
-                            int(reset_kkt_filter), n_steps, int(cfg.revive_on_reset), 0)
+                            int(reset_kkt_filter), n_steps, int(cfg.revive_on_reset),
+                            int(cfg.server_cta_keys), int(cfg.kernel_flags), 0)
         self.ctrl_host.copy_(torch.frombuffer(bytearray(bytes(ctrl)), dtype=torch.uint8))
         self.order_dev[:flat.size].copy_(self.order_host[:flat.size], non_blocking=True)
         self.ctrl_dev.copy_(self.ctrl_host, non_blocking=True)

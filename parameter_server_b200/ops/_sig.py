@@ -16,18 +16,18 @@ CUDA_SIGS = {
     "psb_malloc": "pq", "psb_free": "p", "psb_memset_async": "piqp", "psb_memcpy_async": "ppqp",
     "psb_stream_sync": "p", "psb_host_alloc_pinned": "pq", "psb_host_free_pinned": "p",
     "psb_ipc_get_handle": "pp", "psb_ipc_open_handle": "pp", "psb_ipc_close_handle": "p",
-    "psb_enable_peer_access": "i", "psb_rank_barrier": "piiQp", "psb_rank_barrier_dev": "piipp",
+    "psb_enable_peer_access": "i", "psb_bench_grid_barrier": "piiip", "psb_rank_barrier": "piiQp", "psb_rank_barrier_dev": "piipp",
     # localizer.cu
     "psb_sort_pairs_u64_u32": "ppppqiippp", "psb_sort_pairs_u32_u32": "ppppqiippp",
     "psb_sort_keys_u64": "ppqiippp", "psb_rle_u64": "pqpppppp", "psb_exclusive_sum_i64": "ppqppp",
     "psb_lookup_sorted_u64": "pqpqpp", "psb_lower_bound_u64": "pqpqpp",
     "psb_compact_csr": "pqppqppppppp", "psb_compact_row_ptr": "pqpqqpp",
     "psb_csr_to_csc": "ppppqqqpppppppp",
-    "psb_segments_count": "pqipppp", "psb_segments_fill": "ppqippp", "psb_key_signature": "pqpp",
+    "psb_segments_count": "pqipppp", "psb_segments_fill": "ppqipppp", "psb_key_signature": "pqpp",
     # darlin.cu
     "psb_darlin_pass_begin": "pppp", "psb_darlin_grad_push": "pppiiip",
     "psb_darlin_server_update": "pppiiip", "psb_darlin_pull_update": "pppiiip",
-    "psb_darlin_evaluate": "pppppiQpip", "psb_darlin_fused_pass": "pppppiiipppipp",
+    "psb_darlin_evaluate": "pppppiQpip", "psb_darlin_fused_pass": "pppppiiipppippp",
     "psb_darlin_fused_max_grid": "i", "psb_darlin_enqueue_pass": "ppppiiiippipip",
 }
 _applied = False

@@ -14,7 +14,8 @@ class DarlinCtrl(C.Structure):
     _fields_ = [("kkt_threshold", C.c_double), ("lambda_", C.c_double), ("eta", C.c_double),
                 ("delta_max", C.c_double), ("seq_base", C.c_uint64),
                 ("reset_kkt_filter", C.c_int32), ("n_steps", C.c_int32),
-                ("revive_on_reset", C.c_int32), ("reserved", C.c_int32)]
+                ("revive_on_reset", C.c_int32), ("server_cta_keys", C.c_int32),
+                ("flags", C.c_int32), ("reserved", C.c_int32)]
 
 
 class DarlinProgress(C.Structure):
@@ -31,7 +32,8 @@ class DarlinWorker(C.Structure):
                 ("rank", C.c_int32), ("n_workers", C.c_int32), ("n_servers", C.c_int32),
                 ("land_g", P * MAX_PEERS), ("land_u", P * MAX_PEERS),
                 ("land_cap", C.c_int64 * MAX_PEERS), ("push_flag", P * MAX_PEERS),
-                ("srv_w", P * MAX_PEERS), ("srv_dw", P * MAX_PEERS), ("ver_flag", P)]
+                ("srv_w", P * MAX_PEERS), ("srv_dw", P * MAX_PEERS), ("ver_flag", P),
+                ("seg_meta", P)]
 
 
 class DarlinServer(C.Structure):
@@ -93,7 +95,8 @@ def fused_max_grid(binary: bool) -> int:
 
 
 def fused_pass(wk, sv, ctrl_ptr: int, order_ptr: int, blk_tab_ptr: int, n_steps: int, bps: int,
-               grid: int, bar_ptr: int, out_local: int, out_peer, n_peers: int, scratch_ptr: int):
+               grid: int, bar_ptr: int, out_local: int, out_peer, n_peers: int, scratch_ptr: int,
+               prof_ptr=None):
     check(_lib().psb_darlin_fused_pass(_ref(wk), _ref(sv), ctrl_ptr, order_ptr, blk_tab_ptr,
                                        n_steps, bps, grid, bar_ptr, out_local, out_peer, n_peers,
-                                       scratch_ptr, current_stream()))
+                                       scratch_ptr, prof_ptr, current_stream()))

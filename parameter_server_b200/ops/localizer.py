@@ -134,9 +134,10 @@ def build_segments(col_ptr: torch.Tensor, seg_len: int):
     n_seg = int(col_seg[-1].item())
     seg_col = torch.empty(n_seg, dtype=torch.int32, device=dev)
     seg_beg = torch.empty(n_seg, dtype=torch.int64, device=dev)
+    seg_meta = torch.empty(max(n_seg, 1) * 4, dtype=torch.int32, device=dev)
     check(lib.psb_segments_fill(ptr(col_ptr), ptr(col_seg), n_cols, seg_len, ptr(seg_col),
-                                ptr(seg_beg), current_stream()))
-    return col_seg, seg_col, seg_beg
+                                ptr(seg_beg), ptr(seg_meta), current_stream()))
+    return col_seg, seg_col, seg_beg, seg_meta
 
 
 def key_signature(keys: torch.Tensor) -> int:

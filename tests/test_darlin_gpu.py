@@ -28,14 +28,15 @@ def _oracle_from_csr(data, dictionary, device):
 
 
 def _run_compare(world, binary, tau, passes=4, n_rows=3000, n_feat=700, lam=0.5, tail=0, seed=3,
-                 fused=False, graph=False, expect_filter=True):
+                 fused=False, graph=False, expect_filter=True, server_cta_keys=0):
     from parameter_server_b200.models.darlin import DarlinConfig, DarlinEngine, run_pass_lockstep
     from parameter_server_b200.models.darlin_oracle import OracleServer, run_oracle_pass
     from parameter_server_b200.parallel.comm import run_threads
     from parameter_server_b200.utils.synthetic import make_rcv1_like
     dev = torch.device("cuda:0")
     cfg = DarlinConfig(lambda_l1=lam, max_block_delay=tau, tail_feature_freq=tail,
-                       feature_block_ratio=0.5, seg_len=64, use_graph=graph, seed=seed, fused=fused)
+                       feature_block_ratio=0.5, seg_len=64, use_graph=graph, seed=seed, fused=fused,
+                       server_cta_keys=server_cta_keys)
     shards = [make_rcv1_like(n_rows, n_feat, 24.0, seed=seed, shard=r, device=dev, binary=binary)
               for r in range(world)]
 
@@ -119,6 +120,11 @@ def test_darlin_fused_large_grid_many_segments():
     # more segments than resident warps and long multi-segment columns
     _run_compare(world=1, binary=False, tau=1, n_rows=60000, n_feat=300, fused=True,
                  expect_filter=False)
+
+
+def test_darlin_fused_grid_wide_server_phase():
+    # force the "large step" path: shard update shared by all CTAs between grid barriers
+    _run_compare(world=1, binary=False, tau=2, fused=True, server_cta_keys=1)
 
 
 def test_darlin_graph_train_decreases_objective(tmp_path):

@@ -71,10 +71,16 @@ def test_segments_cover_columns():
     nnz_per_col = torch.tensor([0, 5, 64, 65, 300, 1], device="cuda")
     cp = torch.zeros(7, dtype=torch.int64, device="cuda")
     cp[1:] = torch.cumsum(nnz_per_col, 0)
-    col_seg, seg_col, seg_beg = L.build_segments(cp, 64)
+    col_seg, seg_col, seg_beg, seg_meta = L.build_segments(cp, 64)
     assert col_seg.tolist() == [0, 1, 2, 3, 5, 10, 11]
     assert seg_col.tolist() == [0, 1, 2, 3, 3, 4, 4, 4, 4, 4, 5]
     assert seg_beg.tolist()[3:5] == [int(cp[3]), int(cp[3]) + 64]
+    m = seg_meta.view(-1, 4).tolist()
+    assert [x[0] for x in m] == seg_col.tolist()
+    assert [x[1] & 0xffff for x in m] == [0, 5, 64, 64, 1, 64, 64, 64, 64, 44, 1]
+    assert [(x[1] >> 16) & 1 for x in m] == [1, 1, 1, 1, 0, 1, 0, 0, 0, 0, 1]
+    assert [(x[1] >> 17) & 1 for x in m] == [1, 1, 1, 0, 0, 0, 0, 0, 0, 0, 1]
+    assert [x[2] for x in m] == seg_beg.tolist()
 
 
 def test_key_signature_sensitive_to_content_and_order():
