@@ -1,0 +1,460 @@
+// C ABI of the host runtime for the Python package (ctypes): utilities, parsers, filters and
+// whole in-process clusters.  Everything returns 0 on success; psh_last_error() has the text.
+#include <sstream>
+
+#include "app/linear_method/async_sgd.h"
+#include "app/linear_method/darlin.h"
+#include "app/linear_method/linear.h"
+#include "app/linear_method/model_evaluation.h"
+#include "data/slot_reader.h"
+#include "data/text_parser.h"
+#include "filter/filter.h"
+#include "parameter/kv.h"
+#include "system/heartbeat.h"
+#include "system/monitor.h"
+#include "system/runtime.h"
+#include "util/hash.h"
+#include "util/localizer.h"
+#include "util/sketch.h"
+#include "util/snappy.h"
+
+#define PSH_API extern "C" __attribute__((visibility("default")))
+
+using namespace PS;
+
+static thread_local std::string g_err;
+static int fail(const std::string& m) {
+  g_err = m;
+  return 1;
+}
+static int put(const std::string& s, char* out, int64_t cap, int64_t* len) {
+  if (len) *len = (int64_t)s.size();
+  if ((int64_t)s.size() > cap) return fail("output buffer too small");
+  memcpy(out, s.data(), s.size());
+  return 0;
+}
+
+PSH_API const char* psh_last_error() { return g_err.c_str(); }
+PSH_API int psh_abi_version() { return 1; }
+
+// ---- hashing / compression ------------------------------------------------------------------------
+PSH_API uint32_t psh_crc32c(const char* data, int64_t n) { return crc32c::Value(data, (size_t)n); }
+PSH_API uint32_t psh_crc32c_extend(uint32_t crc, const char* data, int64_t n) { return crc32c::Extend(crc, data, (size_t)n); }
+PSH_API uint32_t psh_murmur3_x86_32(const char* data, int32_t n, uint32_t seed) {
+  uint32_t out;
+  MurmurHash3_x86_32(data, n, seed, &out);
+  return out;
+}
+PSH_API void psh_murmur3_x64_128(const char* data, int32_t n, uint32_t seed, uint64_t* out2) {
+  MurmurHash3_x64_128(data, n, seed, out2);
+}
+PSH_API uint32_t psh_sketch_hash(uint64_t key) { return Sketch::hash(key); }
+PSH_API int64_t psh_snappy_max_compressed(int64_t n) { return (int64_t)snappy::MaxCompressedLength((size_t)n); }
+PSH_API int psh_snappy_compress(const char* src, int64_t n, char* dst, int64_t* out_len) {
+  size_t m = 0;
+  snappy::RawCompress(src, (size_t)n, dst, &m);
+  *out_len = (int64_t)m;
+  return 0;
+}
+PSH_API int psh_snappy_uncompressed_length(const char* src, int64_t n, int64_t* out_len) {
+  size_t m = 0;
+  if (!snappy::GetUncompressedLength(src, (size_t)n, &m)) return fail("bad snappy header");
+  *out_len = (int64_t)m;
+  return 0;
+}
+PSH_API int psh_snappy_uncompress(const char* src, int64_t n, char* dst) {
+  return snappy::RawUncompress(src, (size_t)n, dst) ? 0 : fail("corrupt snappy stream");
+}
+
+// ---- ranges ---------------------------------------------------------------------------------------
+PSH_API void psh_range_even_divide(uint64_t begin, uint64_t end, uint64_t n, uint64_t i, uint64_t* out2) {
+  Range<uint64> r = Range<uint64>(begin, end).evenDivide(n, i);
+  out2[0] = r.begin();
+  out2[1] = r.end();
+}
+
+// ---- text format ----------------------------------------------------------------------------------
+// parse and re-print (single_line=0 -> DebugString); used to check config compatibility
+PSH_API int psh_textproto_normalize(const char* text, int single_line, char* out, int64_t cap, int64_t* len) {
+  PbMsg m;
+  std::string err;
+  if (!m.parse(text, &err)) return fail(err);
+  return put(m.toString(single_line != 0), out, cap, len);
+}
+// value of a dotted path ("linear_method.darlin.max_pass_of_data", "a.b[2].c"); empty if absent
+PSH_API int psh_textproto_get(const char* text, const char* path, char* out, int64_t cap, int64_t* len) {
+  PbMsg m;
+  std::string err;
+  if (!m.parse(text, &err)) return fail(err);
+  const PbMsg* cur = &m;
+  std::string p(path);
+  size_t b = 0;
+  std::string result;
+  while (cur) {
+    // components are separated by '.', but '[...]' extension names contain dots themselves
+    size_t e = b;
+    int depth = 0;
+    while (e < p.size() && (p[e] != '.' || depth > 0)) {
+      if (p[e] == '[' && e == b) depth = 1;
+      if (p[e] == ']') depth = 0;
+      ++e;
+    }
+    std::string comp = p.substr(b, e - b);
+    size_t idx = 0;
+    if (!comp.empty() && comp.back() == ']' && comp[0] != '[') {
+      size_t lb = comp.rfind('[');
+      idx = (size_t)atoi(comp.c_str() + lb + 1);
+      comp = comp.substr(0, lb);
+    }
+    const PbMsg::Field* f = cur->find(comp, idx);
+    if (!f) break;
+    if (e >= p.size()) {
+      result = f->is_msg ? f->msg->shortDebugString() : f->scalar;
+      break;
+    }
+    cur = f->is_msg ? f->msg.get() : nullptr;
+    b = e + 1;
+  }
+  return put(result, out, cap, len);
+}
+
+// ---- parsers --------------------------------------------------------------------------------------
+// Parse `n_lines` newline separated lines; returns a flat description:
+//   per example: n_slots, then per slot: id, n_keys, n_vals ; keys and vals appended to the arrays
+PSH_API int psh_parse_text(const char* text, int32_t format, int32_t ignore_group, int64_t* meta,
+                           int64_t meta_cap, uint64_t* keys, int64_t key_cap, float* vals,
+                           int64_t val_cap, int64_t* counts4) {
+  ExampleParser parser;
+  parser.init((DataConfigView::TextFormat)format, ignore_group != 0);
+  std::istringstream in(text);
+  std::string line;
+  int64_t nm = 0, nk = 0, nv = 0, nex = 0, bad = 0;
+  Example ex;
+  while (std::getline(in, line)) {
+    if (line.empty()) continue;
+    if (!parser.toProto(line.c_str(), &ex)) {
+      ++bad;
+      continue;
+    }
+    if (nm + 1 + 3 * (int64_t)ex.slot.size() > meta_cap) return fail("meta buffer too small");
+    meta[nm++] = ex.slot_size();
+    for (const Slot& s : ex.slot) {
+      meta[nm++] = s.id;
+      meta[nm++] = s.key_size();
+      meta[nm++] = s.val_size();
+      if (nk + s.key_size() > key_cap || nv + s.val_size() > val_cap) return fail("data buffer too small");
+      for (uint64 k : s.key) keys[nk++] = k;
+      for (float v : s.val) vals[nv++] = v;
+    }
+    ++nex;
+  }
+  counts4[0] = nex; counts4[1] = bad; counts4[2] = nk; counts4[3] = nv;
+  return 0;
+}
+
+// Example binary codec round trip (RecordIO payload compatibility)
+PSH_API int psh_example_roundtrip(const char* line, int32_t format, char* out, int64_t cap, int64_t* len) {
+  ExampleParser parser;
+  parser.init((DataConfigView::TextFormat)format, false);
+  Example ex, back;
+  if (!parser.toProto(line, &ex)) return fail("parse error");
+  std::string bin = ex.SerializeAsString();
+  if (!back.ParseFromString(bin)) return fail("binary decode failed");
+  if (back.SerializeAsString() != bin) return fail("binary round trip mismatch");
+  return put(bin, out, cap, len);
+}
+
+// Load text files through SlotReader (columnar cache) and return the slot arrays of one group.
+// info_out receives the merged ExampleInfo as text.
+PSH_API int psh_slot_reader_load(const char* data_conf_text, const char* cache_prefix, char* info_out,
+                                 int64_t cap, int64_t* len) {
+  DataConfig data, cache;
+  std::string err;
+  if (!data.raw()->parse(data_conf_text, &err)) return fail(err);
+  cache.add_file(cache_prefix);
+  SlotReader reader(data, cache);
+  ExampleInfo info;
+  reader.read(&info);
+  return put(info.DebugString(), info_out, cap, len);
+}
+PSH_API int psh_slot_reader_arrays(const char* data_conf_text, const char* cache_prefix, int32_t slot,
+                                   uint64_t* index, int64_t index_cap, int64_t* offset,
+                                   int64_t offset_cap, float* value, int64_t value_cap,
+                                   int64_t* counts3) {
+  DataConfig data, cache;
+  std::string err;
+  if (!data.raw()->parse(data_conf_text, &err)) return fail(err);
+  cache.add_file(cache_prefix);
+  SlotReader reader(data, cache);
+  reader.read(nullptr);
+  SArray<uint64> idx = reader.index(slot);
+  SArray<size_t> off = reader.offset(slot);
+  SArray<float> val = reader.value<float>(slot);
+  counts3[0] = idx.size(); counts3[1] = off.size(); counts3[2] = val.size();
+  if ((int64_t)idx.size() > index_cap || (int64_t)off.size() > offset_cap || (int64_t)val.size() > value_cap)
+    return fail("buffers too small");
+  for (size_t i = 0; i < idx.size(); ++i) index[i] = idx[i];
+  for (size_t i = 0; i < off.size(); ++i) offset[i] = (int64_t)off[i];
+  for (size_t i = 0; i < val.size(); ++i) value[i] = val[i];
+  return 0;
+}
+
+// ---- sketches ---------------------------------------------------------------------------------------
+PSH_API int psh_countmin_filter(const uint64_t* keys, const uint8_t* counts, int64_t n, int32_t cm_n,
+                                int32_t cm_k, int32_t freq, uint8_t* keep_out, uint8_t* table_out) {
+  CountMin<uint64, uint8> cm;
+  cm.resize(cm_n, cm_k, 254);
+  for (int64_t i = 0; i < n; ++i) cm.insert(keys[i], counts[i]);
+  for (int64_t i = 0; i < n; ++i) keep_out[i] = (int)cm.query(keys[i]) > freq;
+  if (table_out) memcpy(table_out, cm.data().data(), cm.n());
+  return 0;
+}
+PSH_API int psh_bloom_fpr(int64_t n_insert, int64_t n_probe, int64_t bits, int32_t k, int32_t blocked,
+                          double* fpr_out) {
+  BloomFilter<uint64> bf((int)bits, k);
+  BlockBloomFilter<uint64> bbf((size_t)bits, k);
+  for (int64_t i = 0; i < n_insert; ++i) {
+    uint64 key = fmix64((uint64)i + 1);
+    if (blocked) bbf.insert(key); else bf.insert(key);
+  }
+  for (int64_t i = 0; i < n_insert; ++i) {
+    uint64 key = fmix64((uint64)i + 1);
+    if (!(blocked ? bbf.query(key) : bf.query(key))) return fail("false negative");
+  }
+  int64_t fp = 0;
+  for (int64_t i = 0; i < n_probe; ++i) {
+    uint64 key = fmix64((uint64)(i + n_insert + 12345));
+    fp += blocked ? bbf.query(key) : bf.query(key);
+  }
+  *fpr_out = (double)fp / (double)n_probe;
+  return 0;
+}
+
+// ---- fixed point codec ------------------------------------------------------------------------------
+PSH_API int psh_fixing_float_roundtrip(const double* in, int64_t n, int32_t nbytes, double min_v,
+                                       double max_v, uint64_t seed, double* out, uint8_t* code_out) {
+  if (nbytes < 1 || nbytes > 7) return fail("nbytes must be in [1,7]");
+  SArray<double> orig(n);
+  for (int64_t i = 0; i < n; ++i) orig[i] = in[i];
+  uint64 s = seed;
+  SArray<char> code = FixingFloatFilter::encodeArray<double>(orig, nbytes, min_v, max_v, &s);
+  if (code_out) memcpy(code_out, code.data(), code.size());
+  SArray<double> back(FixingFloatFilter::decodeArray<double>(code, nbytes, min_v, max_v));
+  for (int64_t i = 0; i < n; ++i) out[i] = back[i];
+  return 0;
+}
+
+// ---- evaluation --------------------------------------------------------------------------------------
+PSH_API int psh_auc_accuracy(const double* label, const double* predict, int64_t n, double* out3) {
+  SArray<double> y(n), p(n);
+  for (int64_t i = 0; i < n; ++i) { y[i] = label[i]; p[i] = predict[i]; }
+  out3[0] = Evaluation<double>::auc(y, p);
+  out3[1] = Evaluation<double>::accuracy(y, p);
+  AUC bucket;
+  bucket.setGoodness(100000);
+  AUCData d;
+  bucket.compute(y, p, d);
+  AUC merged;
+  merged.setGoodness(100000);
+  merged.merge(d);
+  out3[2] = merged.evaluate();
+  return 0;
+}
+
+// ---- whole clusters inside this process ----------------------------------------------------------------
+// Runs 1 scheduler + S servers + W workers as threads over the in-process van (use_tcp=0) or
+// over TCP on localhost ports base_port.. (use_tcp=1) with the given AppConfig text, and
+// returns a report: "iter objective relative nnz_w violation nnz_active\n" per Darlin pass,
+// or "loss auc" for async SGD.
+namespace {
+struct ClusterResult {
+  std::mutex mu;
+  std::string report;
+};
+}  // namespace
+
+PSH_API int psh_run_cluster(const char* app_conf_text, int32_t num_servers, int32_t num_workers,
+                            int32_t use_tcp, int32_t base_port, int32_t message_compression,
+                            char* report_out, int64_t cap, int64_t* len) {
+  std::string conf(app_conf_text);
+  {
+    AppConfig test;
+    std::string err;
+    if (!test.raw()->parse(conf, &err)) return fail("bad app config: " + err);
+  }
+  auto fabric = use_tcp ? shared_ptr<InprocFabric>() : std::make_shared<InprocFabric>();
+  ClusterResult result;
+  auto make_node = [&](const char* role, const std::string& id, int port) {
+    Node n;
+    NodeView::Role r;
+    NodeView::Role_Parse(role, &r);
+    n.set_role(r);
+    n.set_id(id);
+    n.set_hostname("127.0.0.1");
+    n.set_port(port);
+    return n;
+  };
+  Node sched = make_node("SCHEDULER", "H", base_port);
+  std::vector<Node> nodes;
+  nodes.push_back(sched);
+  for (int i = 0; i < num_servers; ++i) nodes.push_back(make_node("SERVER", "S" + to_string(i), base_port + 1 + i));
+  for (int i = 0; i < num_workers; ++i)
+    nodes.push_back(make_node("WORKER", "W" + to_string(i), base_port + 1 + num_servers + i));
+
+  std::vector<std::thread> threads;
+  std::vector<unique_ptr<Postoffice>> offices(nodes.size());
+  for (size_t i = 0; i < nodes.size(); ++i) offices[i].reset(new Postoffice());
+  for (size_t i = 0; i < nodes.size(); ++i) {
+    threads.emplace_back([&, i] {
+      PostofficeOptions opt;
+      opt.my_node = nodes[i];
+      opt.scheduler = sched;
+      opt.num_servers = num_servers;
+      opt.num_workers = num_workers;
+      opt.app_conf = conf;
+      opt.fabric = fabric;
+      opt.message_compression = message_compression != 0;
+      opt.factory = LM::createAppFromText;
+      Postoffice& po = *offices[i];
+      po.start(opt);
+      if (i == 0) {
+        std::ostringstream os;
+        if (auto* d = dynamic_cast<LM::DarlinScheduler*>(po.app())) {
+          for (const auto& kv : d->progress()) {
+            const BCDProgress& p = kv.second;
+            os << kv.first << " " << PbMsg::fmtDouble(p.objective()) << " " << PbMsg::fmtDouble(p.relative_obj())
+               << " " << p.nnz_w() << " " << PbMsg::fmtDouble(p.violation()) << " " << p.nnz_active_set() << "\n";
+          }
+        } else if (auto* s = dynamic_cast<LM::AsyncSGDScheduler*>(po.app())) {
+          os << PbMsg::fmtDouble(s->lastLoss()) << " " << PbMsg::fmtDouble(s->lastAUC()) << "\n";
+        } else if (auto* e = dynamic_cast<LM::ModelEvaluation*>(po.app())) {
+          os << PbMsg::fmtDouble(e->auc()) << " " << PbMsg::fmtDouble(e->accuracy()) << " " << e->numExamples() << "\n";
+        }
+        Lock l(result.mu);
+        result.report = os.str();
+      }
+      po.stop();
+    });
+  }
+  for (auto& t : threads) t.join();
+  offices.clear();
+  return put(result.report, report_out, cap, len);
+}
+
+// hello-world style KV check on an in-process cluster: servers hold keys 0..n-1 with value
+// 0.1*key in a KVVector, each worker pulls `pull_keys`; returns the pulled values of worker 0
+namespace {
+class KVServerApp : public App {
+ public:
+  KVServerApp(const string& name, int n) : App(name), vec_("w", name), n_(n) {}
+  ~KVServerApp() { stopExecutor(); }
+  void init() override {
+    Range<Key> mine = myKeyRange();
+    SArray<Key> key;
+    SArray<float> val;
+    for (Key k = 0; k < (Key)n_; ++k)
+      if (mine.contains(k)) { key.pushBack(k); val.pushBack(0.1f * k); }
+    vec_.key() = key;
+    vec_.value() = val;
+  }
+  KVVector<Key, float> vec_;
+  int n_;
+};
+class KVWorkerApp : public App {
+ public:
+  KVWorkerApp(const string& name, std::vector<uint64> keys, std::vector<float>* out, std::mutex* mu)
+      : App(name), vec_("w", name), keys_(keys), out_(out), mu_(mu) {}
+  ~KVWorkerApp() { stopExecutor(); }
+  void run() override {
+    SArray<Key> key;
+    for (uint64 k : keys_) key.pushBack(k);
+    vec_.key() = key;
+    // push +1 to every key, then pull
+    MessagePtr push(new Message(kServerGroup));
+    push->setKey(key);
+    SArray<float> ones(key.size(), 1.0f);
+    push->addValue(ones);
+    push->addFilter(FilterConfigView::KEY_CACHING);
+    int tp = vec_.push(push);
+    vec_.waitOutMsg(kServerGroup, tp);
+    MessagePtr msg(new Message(kServerGroup));
+    msg->setKey(key);
+    msg->addFilter(FilterConfigView::KEY_CACHING);
+    int t = vec_.pull(msg);
+    vec_.waitOutMsg(kServerGroup, t);
+    if (myRank() == 0) {
+      Lock l(*mu_);
+      SArray<float> v = vec_.value();
+      out_->assign(v.begin(), v.end());
+    }
+  }
+  KVVector<Key, float> vec_;
+  std::vector<uint64> keys_;
+  std::vector<float>* out_;
+  std::mutex* mu_;
+};
+}  // namespace
+
+PSH_API int psh_run_kv_cluster(int32_t num_servers, int32_t num_workers, int32_t n_keys,
+                               const uint64_t* pull_keys, int32_t n_pull, int32_t use_tcp,
+                               int32_t base_port, float* out_vals) {
+  auto fabric = use_tcp ? shared_ptr<InprocFabric>() : std::make_shared<InprocFabric>();
+  std::vector<uint64> keys(pull_keys, pull_keys + n_pull);
+  std::vector<float> got;
+  std::mutex mu;
+  auto factory = [&](const string& name, const string&) -> App* {
+    NodeView me = Postoffice::current().myNode();
+    if (me.role() == NodeView::SERVER) return new KVServerApp(name, n_keys);
+    if (me.role() == NodeView::WORKER) return new KVWorkerApp(name, keys, &got, &mu);
+    return new App(name);
+  };
+  std::vector<Node> nodes;
+  auto add = [&](NodeView::Role r, const std::string& id, int port) {
+    Node n;
+    n.set_role(r);
+    n.set_id(id);
+    n.set_hostname("127.0.0.1");
+    n.set_port(port);
+    nodes.push_back(n);
+  };
+  add(NodeView::SCHEDULER, "H", base_port);
+  for (int i = 0; i < num_servers; ++i) add(NodeView::SERVER, "S" + to_string(i), base_port + 1 + i);
+  for (int i = 0; i < num_workers; ++i) add(NodeView::WORKER, "W" + to_string(i), base_port + 1 + num_servers + i);
+  std::vector<unique_ptr<Postoffice>> offices(nodes.size());
+  for (auto& o : offices) o.reset(new Postoffice());
+  std::vector<std::thread> threads;
+  for (size_t i = 0; i < nodes.size(); ++i) {
+    threads.emplace_back([&, i] {
+      PostofficeOptions opt;
+      opt.my_node = nodes[i];
+      opt.scheduler = nodes[0];
+      opt.num_servers = num_servers;
+      opt.num_workers = num_workers;
+      opt.fabric = fabric;
+      opt.factory = factory;
+      offices[i]->start(opt);
+      offices[i]->stop();
+    });
+  }
+  for (auto& t : threads) t.join();
+  offices.clear();
+  if ((int)got.size() != n_pull) return fail("worker 0 pulled " + to_string(got.size()) + " values");
+  for (int i = 0; i < n_pull; ++i) out_vals[i] = got[i];
+  return 0;
+}
+
+// ---- diagnostics ---------------------------------------------------------------------------------------
+#include <execinfo.h>
+#include <signal.h>
+static void psh_crash_handler(int sig) {
+  void* bt[64];
+  int n = backtrace(bt, 64);
+  fprintf(stderr, "psb200 host runtime: fatal signal %d\n", sig);
+  backtrace_symbols_fd(bt, n, 2);
+  _exit(128 + sig);
+}
+// print a native backtrace on SIGSEGV / SIGABRT (tests and tools call this first)
+PSH_API void psh_install_crash_handler() {
+  signal(SIGSEGV, psh_crash_handler);
+  signal(SIGABRT, psh_crash_handler);
+}

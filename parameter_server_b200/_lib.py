@@ -35,7 +35,9 @@ def _load(name: str) -> ctypes.CDLL:
         raise NativeError(
             f"{path} is missing: run `python -m parameter_server_b200.build` "
             "(the kernels have no PyTorch fallback)")
-    return ctypes.CDLL(str(path), mode=ctypes.RTLD_GLOBAL)
+    # RTLD_LOCAL: the libraries carry their own (static) C++ runtime, which must not interpose
+    # with the libstdc++ that torch brings into the process
+    return ctypes.CDLL(str(path), mode=ctypes.RTLD_LOCAL)
 
 
 def cuda_lib() -> ctypes.CDLL:

@@ -74,7 +74,8 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path:
         list(ex.map(lambda j: _run(j[0], j[1], verbose), jobs))
     out = LIBDIR / "libpsb200_cuda.so"
     if force or jobs or not out.exists():
-        _run([nvcc, "-shared", "-o", str(out), *map(str, objs), "-lcudart"], None, verbose)
+        _run([nvcc, "-shared", "-o", str(out), *map(str, objs), "-lcudart",
+              "-Xlinker", "--exclude-libs,ALL", "-Xlinker", "-Bsymbolic"], None, verbose)
     return out
 
 
@@ -100,7 +101,8 @@ def build_host(force: bool = False, verbose: bool = False) -> Path | None:
         list(ex.map(lambda j: _run(j[0], j[1], verbose), jobs))
     out = LIBDIR / "libpsb200_host.so"
     if force or jobs or not out.exists():
-        _run([cxx, "-shared", "-o", str(out), *map(str, lib_objs), "-lz", "-pthread", "-ldl"],
+        _run([cxx, "-shared", "-o", str(out), *map(str, lib_objs), "-lz", "-pthread", "-ldl",
+              "-Wl,--exclude-libs,ALL", "-Wl,-Bsymbolic"],
              None, verbose)
     for name, o in mains:
         exe = BINDIR / name
