@@ -220,6 +220,7 @@ class AsyncSGDWorker : public ISGDCompNode, public LinearMethod {
       w.setZero();
     }
     SArray<V> Xw = X->times(w);
+    if (getenv("PSB_DEBUG_SGD")) fprintf(stderr, "dbg id=%d rows=%zu cols=%zu nnz=%zu |w|0=%zu wsum=%g Xw0=%g y0=%g keys=%zu\n", id, X->rows(), X->cols(), X->nnz(), w.nnz(), w.sum(), (double)Xw[0], (double)Y->value()[0], model_.key(id).size());
     SGDProgress prog;
     prog.add_objective(loss_->evaluate(Y->value(), Xw));
     prog.add_auc(Evaluation<V>::auc(Y->value(), Xw));

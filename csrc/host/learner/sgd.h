@@ -54,10 +54,13 @@ class ISGDScheduler : public App {
       fprintf(stderr, " sec  examples    loss      auc   accuracy   |w|_0  updt ratio\n");
       show_prog_head_ = false;
     }
-    last_loss_ = num_ex ? objv.sum() / (double)num_ex : 0;
-    last_auc_ = auc.mean();
+    if (num_ex) {  // server-only reports carry model statistics but no loss
+      last_loss_ = objv.sum() / (double)num_ex;
+      last_auc_ = auc.mean();
+    }
     fprintf(stderr, "%4d  %.2e  %.3e  %.4f  %.4f  %.2e  %.2e\n", (int)time,
-            (double)num_ex_processed_, last_loss_, last_auc_, acc.mean(), (double)nnz_w,
+            (double)num_ex_processed_, num_ex ? objv.sum() / (double)num_ex : 0.0, auc.mean(),
+            acc.mean(), (double)nnz_w,
             sqrt(delta_sum) / sqrt(std::max(weight_sum, 1e-300)));
   }
 

@@ -52,7 +52,8 @@ def _planted_model(n_features: int, seed: int, density: float = 0.02, device="cp
 
 def make_rcv1_like(n_rows: int = RCV1_EXAMPLES, n_features: int = RCV1_FEATURES,
                    nnz_per_row: float = RCV1_NNZ_PER_ROW, seed: int = 0, shard: int = 0,
-                   device="cpu", binary: bool = False, noise: float = 0.5) -> SparseCSR:
+                   device="cpu", binary: bool = False, noise: float = 0.5,
+                   model_density: float | None = None) -> SparseCSR:
     """One worker's shard of an rcv1-shaped dataset.
 
     `seed` fixes the feature popularity permutation and the planted model (shared by all
@@ -88,7 +89,9 @@ def make_rcv1_like(n_rows: int = RCV1_EXAMPLES, n_features: int = RCV1_FEATURES,
         sq = torch.zeros(n_rows, dtype=torch.float32, device=dev).index_add_(0, row, v * v)
         vals = v / sq.sqrt().clamp_min(1e-12)[row]
         xv = vals.double()
-    w_true = _planted_model(n_features, seed, device=dev)
+    if model_density is None:  # enough planted features that nearly every row carries signal
+        model_density = min(0.5, max(0.02, 8.0 / max(nnz_per_row, 1.0) ))
+    w_true = _planted_model(n_features, seed, density=model_density, device=dev)
     margin = torch.zeros(n_rows, dtype=torch.float64, device=dev).index_add_(0, row, xv * w_true[fid])
     margin = margin / margin.std().clamp_min(1e-12) * 2.0
     margin = margin + noise * torch.randn(n_rows, generator=g, device=dev, dtype=torch.float64)
@@ -116,7 +119,7 @@ def make_ctr_like(n_rows: int, n_groups: int = 8, keys_per_group: int = 1 << 20,
         row = torch.div(comb, keys_per_group, rounding_mode="floor")
         rank = comb - row * keys_per_group
         # multiplicative hash into 54 bits, group id in the top 10 bits
-        h = (rank * 0x9E3779B97F4A7C15 + grp * 0x632BE59BD9B4E019) & ((1 << 54) - 1)
+        h = (rank * (0x9E3779B97F4A7C15 - (1 << 64)) + grp * 0x632BE59BD9B4E019) & ((1 << 54) - 1)
         keys = h | (grp << 54)
         wg = _planted_model(keys_per_group, seed + grp, density=0.01, device=dev)
         margin.index_add_(0, row, wg[rank])
@@ -142,3 +145,19 @@ def write_libsvm(data: SparseCSR, path: str) -> None:
         for r in range(data.n_rows):
             items = sorted((keys[e], 1.0 if vals is None else vals[e]) for e in range(rp[r], rp[r + 1]))
             f.write(("+1" if y[r] > 0 else "-1") + "".join(f" {k}:{v:.6g}" for k, v in items) + "\n")
+
+
+def write_ps_sparse_binary(groups: dict, path: str) -> None:
+    """Dump {group: SparseCSR} as PS SPARSE_BINARY text: `label; grp key key ...; grp ...;`."""
+    gids = sorted(groups)
+    y = groups[gids[0]].y.cpu().tolist()
+    rps = {g: groups[g].row_ptr.cpu().tolist() for g in gids}
+    keys = {g: [k & 0xFFFFFFFFFFFFFFFF for k in groups[g].keys.cpu().tolist()] for g in gids}
+    with open(path, "w") as f:
+        for r in range(len(y)):
+            parts = ["1" if y[r] > 0 else "-1"]
+            for g in gids:
+                ks = keys[g][rps[g][r]:rps[g][r + 1]]
+                if ks:
+                    parts.append(f" {g} " + " ".join(str(k) for k in sorted(ks)))
+            f.write(";".join(parts) + ";\n")

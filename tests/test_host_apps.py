@@ -1,0 +1,156 @@
+"""End-to-end runs of the native parameter server (scheduler + servers + workers as threads of
+one process): Darlin against the PyTorch oracle, async SGD / FTRL, model evaluation."""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from parameter_server_b200.runtime import host
+from parameter_server_b200.utils.range import Range
+from parameter_server_b200.utils.synthetic import make_rcv1_like, write_libsvm
+
+N_FILES, ROWS, FEATS, NNZ = 4, 1500, 600, 20.0
+
+
+@pytest.fixture(scope="module")
+def dataset(tmp_path_factory):
+    d = tmp_path_factory.mktemp("rcv1")
+    os.makedirs(d / "train")
+    shards = []
+    for p in range(N_FILES):
+        s = make_rcv1_like(ROWS, FEATS, NNZ, seed=3, shard=p)
+        write_libsvm(s, str(d / "train" / f"part-{p}"))
+        shards.append(s)
+    return d, shards
+
+
+def _conf(d, body, extra_data=""):
+    return f'''
+linear_method {{
+  training_data {{ format: TEXT text: LIBSVM file: "{d}/train/part.*" {extra_data} }}
+  model_output {{ format: TEXT file: "{d}/model/m" }}
+  loss {{ type: LOGIT }}
+  {body}
+}}'''
+
+
+def _darlin_conf(d, passes=5, tau=0, random_order=False, lam=0.5, cache="c", ratio=0.5):
+    return _conf(d, f'''
+  penalty {{ type: L1 lambda: {lam} }}
+  learning_rate {{ type: CONSTANT alpha: 1 }}
+  darlin {{ max_pass_of_data: {passes} epsilon: 1e-7 feature_block_ratio: {ratio} max_block_delay: {tau}
+           random_feature_block_order: {"true" if random_order else "false"}
+           local_cache {{ format: BIN file: "{d}/cache/{cache}" }} }}''')
+
+
+def _report(text):
+    rows = [l.split() for l in text.strip().splitlines()]
+    return [dict(it=int(r[0]), obj=float(r[1]), rel=float(r[2]), nnz=int(r[3]), vio=float(r[4]),
+                 active=int(r[5])) for r in rows]
+
+
+def _oracle_trajectory(shards, n_workers, passes, lam):
+    """The same schedule on the PyTorch oracle: files round robin over the workers, blocks from
+    the merged slot statistics, sequential block order, KKT threshold = vio / n * 10."""
+    from parameter_server_b200.models.darlin_oracle import DarlinOracle, OracleServer, run_oracle_pass
+    # values are written with 6 significant digits: re-read them the way the parser sees them
+    def quant(s):
+        v = torch.tensor([float("%.6g" % x) for x in s.vals.tolist()], dtype=torch.float32)
+        return v
+    per_worker = [[] for _ in range(n_workers)]
+    for i, s in enumerate(shards):
+        per_worker[i % n_workers].append(s)
+    dictionary = torch.unique(torch.cat([s.keys for s in shards]))
+    workers = []
+    for parts in per_worker:
+        rows, cols, vals, ys, base = [], [], [], [], 0
+        for s in parts:
+            r = torch.repeat_interleave(torch.arange(s.n_rows), s.row_ptr[1:] - s.row_ptr[:-1]) + base
+            rows.append(r); cols.append(torch.searchsorted(dictionary, s.keys)); vals.append(quant(s))
+            ys.append(s.y); base += s.n_rows
+        row, col, val, y = torch.cat(rows), torch.cat(cols), torch.cat(vals), torch.cat(ys)
+        order = torch.argsort(col * base + row)
+        row, col, val = row[order], col[order], val[order]
+        cp = torch.zeros(dictionary.numel() + 1, dtype=torch.int64)
+        cp[1:] = torch.cumsum(torch.bincount(col, minlength=dictionary.numel()), 0)
+        workers.append(DarlinOracle(cp, row, val, y, base))
+    nnz_ele = sum(s.nnz for s in shards)
+    n_ex = sum(s.n_rows for s in shards)
+    n = max(int(math.ceil(nnz_ele / n_ex * 0.5)), 1)
+    kmin, kmax = int(dictionary[0]), int(dictionary[-1]) + 1
+    blocks = []
+    for i in range(n):
+        r = Range(kmin, kmax).even_divide(n, i)
+        lo = int(torch.searchsorted(dictionary, torch.tensor(r.begin)))
+        hi = int(torch.searchsorted(dictionary, torch.tensor(r.end)))
+        if r.end > r.begin:
+            blocks.append((lo, hi))
+    server = OracleServer(dictionary.numel(), "cpu", lam)
+    thr, reset, out = 1e20, False, []
+    for it in range(passes):
+        ev = run_oracle_pass(workers, server, blocks, list(range(len(blocks))), thr, reset)
+        out.append(ev)
+        thr = ev["violation"] / n_ex * 10
+    return out, len(blocks)
+
+
+@pytest.mark.parametrize("tcp", [False, True])
+def test_darlin_cluster_matches_oracle(dataset, tcp):
+    d, shards = dataset
+    rep = _report(host.run_cluster(_darlin_conf(d, cache="tcp" if tcp else "inproc"), 2, 2, tcp=tcp,
+                                   base_port=19700 + os.getpid() % 200))
+    ref, n_blocks = _oracle_trajectory(shards, 2, 5, 0.5)
+    assert n_blocks == 10 and len(rep) == 5
+    for a, b in zip(rep, ref):
+        assert a["obj"] == pytest.approx(b["objective"], rel=1e-9)
+        assert a["nnz"] == b["nnz_w"] and a["active"] == b["nnz_active"]
+        assert a["vio"] == pytest.approx(b["violation"], rel=1e-9, abs=1e-12)
+    assert rep[-1]["active"] < rep[0]["active"]          # the KKT filter shrank the active set
+    # one model file per server, key<TAB>value, only non-zero weights
+    files = sorted(os.listdir(d / "model"))
+    assert files == ["m_S0", "m_S1"]
+    n_lines = sum(len(open(d / "model" / f).read().splitlines()) for f in files)
+    assert n_lines == rep[-1]["nnz"]
+
+
+def test_darlin_bounded_delay_random_order_and_slot_cache(dataset):
+    d, _ = dataset
+    # the second run over the same cache prefix must hit the columnar slot cache
+    host.run_cluster(_darlin_conf(d, passes=2, cache="again"), 1, 2)
+    assert any(f.endswith(".info") for f in os.listdir(d / "cache"))
+    base = _report(host.run_cluster(_darlin_conf(d, passes=6, cache="again", ratio=3), 2, 3))
+    # 60 blocks, at most 3 in flight: staleness is small next to the number of blocks
+    tau = _report(host.run_cluster(_darlin_conf(d, passes=6, tau=2, random_order=True, cache="again", ratio=3),
+                                   2, 3, message_compression=False))
+    objs = [r["obj"] for r in tau]
+    assert all(b < a for a, b in zip(objs, objs[1:]))
+    assert objs[-1] == pytest.approx(base[-1]["obj"], rel=2e-2)
+
+
+def test_async_sgd_ftrl_and_model_evaluation(dataset):
+    d, _ = dataset
+    conf = _conf(d, '''
+  penalty { type: L1 lambda: .01 lambda: .001 }
+  learning_rate { type: DECAY alpha: .5 beta: 1 }
+  async_sgd { algo: FTRL minibatch: 200 num_data_pass: 4 max_delay: 2 report_interval: 0 }''')
+    loss, auc = map(float, host.run_cluster(conf, 2, 2).split())
+    assert loss < 0.55 and auc > 0.85      # log 2 = 0.693 is the loss of the zero model
+    ev = f'''linear_method {{
+      validation_data {{ format: TEXT text: LIBSVM file: "{d}/train/part.*" }}
+      model_input {{ format: TEXT file: "{d}/model/m_S.*" }} }}'''
+    auc2, acc, n = host.run_cluster(ev, 0, 0).split()
+    assert int(n) == N_FILES * ROWS and float(auc2) > 0.85 and float(acc) > 0.75
+
+
+@pytest.mark.parametrize("algo,extra", [("STANDARD", "ada_grad: true"), ("STANDARD", "ada_grad: false"),
+                                       ("FTRL", "fixing_float_by_nbytes: 2")])
+def test_async_sgd_variants_learn(dataset, algo, extra):
+    d, _ = dataset
+    conf = _conf(d, f'''
+  penalty {{ type: L2 lambda: .0001 }}
+  learning_rate {{ type: DECAY alpha: .5 beta: 1 }}
+  async_sgd {{ algo: {algo} {extra} minibatch: 300 num_data_pass: 3 report_interval: 0 tail_feature_freq: 1 }}''')
+    loss, auc = map(float, host.run_cluster(conf, 1, 2).split())
+    assert loss < 0.66 and auc > 0.75
