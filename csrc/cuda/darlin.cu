@@ -25,6 +25,7 @@
 //     can be processed by independent warps without reading a half-updated cached w.
 #include "common.cuh"
 #include "../../include/psb200.h"
+#include <mutex>
 
 namespace psb {
 
@@ -1124,5 +1125,67 @@ PSB_API int psb_darlin_fused_pass(const psb_darlin_worker* wk, const psb_darlin_
       ? (single ? (const void*)k_darlin_pass<false, true> : (const void*)k_darlin_pass<false, false>)
       : (single ? (const void*)k_darlin_pass<true, true> : (const void*)k_darlin_pass<true, false>);
   PSB_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), args, 0, (cudaStream_t)stream));
+  return 0;
+}
+
+// -------------------------------------------------------------------------------------------
+// Progress evaluation for callers that must not allocate.
+//
+// psb_darlin_evaluate needs a scratch buffer (one set of partial sums per CTA plus an arrival
+// counter) that the caller allocates.  Some callers cannot do that: a monitoring thread inside
+// a training job that has already handed all of HBM to its own pools (a cudaMalloc there fails
+// or fragments the shard layout), or a latency-sensitive loop that must not take the
+// allocator's lock and the device-wide synchronisation cudaMalloc / cudaFree may imply.  For
+// them the scratch lives in the library image: one fixed array per GPU that loads this
+// library, held until the process exits.
+//
+// In host code the array's name is only a handle: passing it to a kernel would hand over a
+// host-side address.  Its device address is looked up once per device with
+// cudaGetSymbolAddress while that device is current, and that address is what the kernel gets.
+// -------------------------------------------------------------------------------------------
+#define PSB_DARLIN_EVAL_NOALLOC_MAX_GRID 1024
+namespace psb {
+constexpr size_t kEvalNoallocBytes =
+    (size_t)PSB_DARLIN_EVAL_NOALLOC_MAX_GRID * 4 * sizeof(double) + 256;
+static __device__ __align__(256) unsigned char g_eval_noalloc_scratch[kEvalNoallocBytes];
+
+static std::mutex g_eval_noalloc_mu;
+static double* g_eval_noalloc_ptr[64] = {nullptr};
+}  // namespace psb
+
+PSB_API int32_t psb_darlin_evaluate_noalloc_max_grid(void) { return PSB_DARLIN_EVAL_NOALLOC_MAX_GRID; }
+
+PSB_API int psb_darlin_evaluate_noalloc(const psb_darlin_worker* wk, const psb_darlin_server* sv,
+                                        const psb_darlin_ctrl* ctrl, psb_darlin_progress* out_local,
+                                        uint64_t seq, int32_t grid, void* stream) {
+  PSB_REQUIRE(ctrl && out_local, "psb_darlin_evaluate_noalloc: ctrl and out_local are required");
+  PSB_REQUIRE(grid >= 1, "psb_darlin_evaluate_noalloc: grid=%d", grid);
+  PSB_REQUIRE(grid <= PSB_DARLIN_EVAL_NOALLOC_MAX_GRID,
+              "psb_darlin_evaluate_noalloc: grid=%d exceeds the maximum of %d CTAs that the fixed "
+              "%zu-byte scratch array can serve; use psb_darlin_evaluate with your own scratch",
+              grid, PSB_DARLIN_EVAL_NOALLOC_MAX_GRID, kEvalNoallocBytes);
+  int dev = 0;
+  PSB_CUDA(cudaGetDevice(&dev));
+  PSB_REQUIRE(dev >= 0 && dev < 64, "psb_darlin_evaluate_noalloc: device ordinal %d unsupported", dev);
+  double* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_eval_noalloc_mu);
+    if (!g_eval_noalloc_ptr[dev]) {
+      // set-up, once per device and with that device current
+      void* p = nullptr;
+      PSB_CUDA(cudaGetSymbolAddress(&p, g_eval_noalloc_scratch));
+      PSB_REQUIRE(p != nullptr, "psb_darlin_evaluate_noalloc: no device address for the scratch array");
+      g_eval_noalloc_ptr[dev] = static_cast<double*>(p);
+    }
+    scratch = g_eval_noalloc_ptr[dev];
+  }
+  // the array keeps whatever the previous call left: the arrival counter behind the partial
+  // sums has to start at zero (the partial sums themselves are fully rewritten by every call)
+  PSB_CUDA(cudaMemsetAsync(scratch + 4 * (size_t)grid, 0, 16, (cudaStream_t)stream));
+  k_evaluate<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+      wk ? wk->z : nullptr, wk ? wk->n_rows : 0, sv ? sv->w : nullptr,
+      sv ? sv->active : nullptr, sv ? sv->n_keys : 0, sv ? sv->violation : nullptr, ctrl,
+      out_local, nullptr, 0, seq, scratch);
+  PSB_LAUNCH_CHECK();
   return 0;
 }

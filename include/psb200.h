@@ -155,6 +155,23 @@ int psb_darlin_enqueue_pass(const psb_darlin_worker* wk, const psb_darlin_server
                             psb_darlin_progress* const* out_peer, int32_t n_peers,
                             double* eval_scratch, int32_t grid_eval, void* stream);
 
+/* Progress evaluation that allocates nothing (no counterpart in the reference, whose nodes are
+ * ordinary CPU processes free to malloc).  Same result as psb_darlin_evaluate, but the scratch
+ * (per-CTA partial sums + arrival counter) is a fixed array inside the library image instead of
+ * a caller buffer.  Meant for callers that cannot allocate device memory: code running inside a
+ * job whose HBM is already fully committed to its own pools, or a latency-sensitive thread that
+ * must avoid the allocator lock and the device-wide synchronisation an allocation can imply.
+ *   - limit: grid <= psb_darlin_evaluate_noalloc_max_grid() (1024 CTAs, 33 KB of scratch that
+ *     every GPU loading the library holds until exit); larger grids are rejected with an error;
+ *   - the first call on a device looks up the array's device address (one-time set-up with that
+ *     device current); make that first call before starting any stream capture;
+ *   - all calls on a device share the one array: calls that overlap on the GPU (different
+ *     streams) race on it, so serialise them; nothing is written to peers (out_local only). */
+int32_t psb_darlin_evaluate_noalloc_max_grid(void);
+int psb_darlin_evaluate_noalloc(const psb_darlin_worker* wk, const psb_darlin_server* sv,
+                                const psb_darlin_ctrl* ctrl, psb_darlin_progress* out_local,
+                                uint64_t seq, int32_t grid, void* stream);
+
 /* Whole pass in ONE cooperative launch: pass_begin, every step and the evaluation run inside
  * a persistent kernel whose phases are separated by grid barriers; with one rank the shard
  * update is applied by the warp that completes a column's gradient.  `bar`: 4 zeroed uint32
