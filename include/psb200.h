@@ -186,6 +186,118 @@ int psb_darlin_fused_pass(const psb_darlin_worker* wk, const psb_darlin_server* 
                           psb_darlin_progress* const* out_peer, int32_t n_peers, double* scratch,
                           uint64_t* prof, void* stream);
 
+
+/* ------------------------------------------------------------------------- *
+ *  Asynchronous minibatch SGD (FTRL / AdaGrad / SGD) on a sharded hash store
+ *  ref: src/app/linear_method/async_sgd.h, src/parameter/kv_store.h, src/learner/sgd.h
+ * ------------------------------------------------------------------------- */
+
+/* One minibatch on a worker: CSR over the minibatch's local columns (= its sorted unique keys),
+ * the (owner, slot) of every column in the owners' tables, and the peer views needed to pull
+ * weights and to push gradients.  A worker owns a ring of `depth` landing regions on every
+ * server (depth = max_delay + 1): push `seq` goes to region seq % depth once the server
+ * acknowledged push seq - depth. */
+typedef struct psb_sgd_worker {
+  const int64_t* row_ptr;      /* [n_rows+1] */
+  const uint32_t* col;         /* [nnz] local column */
+  const float* val;            /* [nnz] or NULL (binary features) */
+  const float* y;              /* [n_rows] */
+  int64_t n_rows, n_cols;
+  const int32_t* col_owner;    /* [n_cols] */
+  const int64_t* col_slot;     /* [n_cols] slot in the owner's table (-1: unknown key, weight 0) */
+  const int64_t* owner_begin;  /* [n_servers+1] columns are sorted by key, so owners are segments */
+  float* w_local;              /* [n_cols] pulled weights */
+  float* g_local;              /* [n_cols] gradient */
+  float* xw;                   /* [n_rows] margins (kept for AUC) */
+  double* stats;               /* [3] += loss, correct predictions, rows */
+  const float* tab_w[PSB_MAX_PEERS];    /* server s: weight array of its table */
+  int32_t* land_slot[PSB_MAX_PEERS];    /* on server s, this worker's ring: [depth][land_cap] */
+  float* land_val[PSB_MAX_PEERS];
+  int8_t* land_q[PSB_MAX_PEERS];
+  float* land_scale[PSB_MAX_PEERS];     /* [depth][land_cap/128+1] */
+  int64_t* land_cnt[PSB_MAX_PEERS];     /* on server s: [depth] counts of this worker */
+  uint64_t* land_flag[PSB_MAX_PEERS];   /* on server s: &flag[rank] */
+  const uint64_t* ack;                  /* local: [n_servers], written by the servers */
+  int64_t land_cap;
+  int32_t rank, n_workers, n_servers, depth;
+  int32_t loss;    /* LossConfig::Type: 1 SQUARE, 2 LOGIT, 4 SQUARE_HINGE */
+  int32_t quant;   /* 0: fp32 push; 1: int8 with one fp32 scale per 128 values */
+} psb_sgd_worker;
+
+typedef struct psb_sgd_server {
+  float* w;                  /* table arrays, [cap] */
+  float* z;                  /* FTRL: z; AdaGrad: sum of squared gradients */
+  float* n;                  /* FTRL: sqrt(n) */
+  int64_t cap;
+  const int32_t* land_slot;  /* [n_workers][depth][land_cap] */
+  const float* land_val;
+  const int8_t* land_q;
+  const float* land_scale;   /* [n_workers][depth][land_cap/128+1] */
+  const int64_t* land_cnt;   /* [n_workers][depth] */
+  const uint64_t* land_flag; /* [n_workers] */
+  uint64_t* ack_out[PSB_MAX_PEERS];  /* on worker w: &ack_w[rank] */
+  int64_t land_cap;
+  double* stats;             /* [3] += change of nnz(w), sum w^2, sum (w_new-w_old)^2 of touched keys */
+  int32_t rank, n_workers, depth;
+  int32_t algo;              /* 0 FTRL, 1 AdaGrad, 2 SGD */
+  int32_t quant;
+  float alpha, beta, l1, l2;
+  float sgd_t;               /* sqrt(iteration) for the plain SGD step size */
+} psb_sgd_server;
+
+/* table set-up and key resolution (K8a).  Capacities are powers of two. */
+int psb_kv_table_clear(uint64_t* keys, int64_t cap, void* stream);
+int psb_kv_lookup_insert(const uint64_t* keys, int64_t n, const int32_t* owner,
+                         uint64_t* const* table_keys_host, const int64_t* cap_host, int32_t n_servers,
+                         int64_t* slot_out, int32_t* overflow_dev, void* stream);
+int psb_kv_export_nonzero(const uint64_t* keys, const float* w, int64_t cap, uint64_t* out_keys,
+                          float* out_w, uint64_t* count_dev, void* stream);
+/* K6+K7+C3+C4: pull, margins / loss / gradient, push of one minibatch in one cooperative launch.
+ * `bar`: one zeroed uint32.  seq starts at 1 and increases by one per step. */
+int psb_sgd_max_grid(void);
+int psb_sgd_worker_step(const psb_sgd_worker* wk, uint64_t seq, int32_t grid, uint32_t* bar,
+                        void* stream);
+/* K8: wait (on the device) for push `seq` of every worker, apply them in worker order, then
+ * acknowledge to the workers. */
+int psb_sgd_server_update(const psb_sgd_server* sv, uint64_t seq, int32_t grid, void* stream);
+
+
+/* ------------------------------------------------------------------------- *
+ *  Evaluation, sketches, codecs, fills (eval.cu)
+ * ------------------------------------------------------------------------- */
+/* K14 exact AUC (ref src/util/evaluation.h:22-48): sort by prediction, area = sum over negatives of
+ * the positives ranked below.  work_f: float[2n], work_i: int64[n], out_dev: double[2] zeroed by the
+ * caller -> {area, #positives}; AUC = area / (pos * (n - pos)), flipped when < 0.5. CUB temp convention. */
+int psb_auc_exact(const float* label, const float* predict, int64_t n, float* work_f, int64_t* work_i,
+                  double* out_dev, void* temp, int64_t* temp_bytes, void* stream);
+/* out_dev: double[2] zeroed by the caller -> {#correct, total logloss} (ref evaluation.h:52-63) */
+int psb_accuracy_logloss(const float* label, const float* predict, int64_t n, float threshold,
+                         double* out_dev, void* stream);
+/* K13 CountMin with saturating 8-bit counters, hash and probe sequence identical to the host
+ * sketch (ref src/util/countmin.h:21-41, sketch.h:20-33, frequency_filter.h:26-43) */
+int psb_countmin_insert(const uint64_t* keys, const uint32_t* counts, int64_t n, uint8_t* table,
+                        int32_t cm_n, int32_t cm_k, void* stream);
+int psb_countmin_query(const uint64_t* keys, int64_t n, const uint8_t* table, int32_t cm_n, int32_t cm_k,
+                       int32_t freq, uint8_t* keep_out, void* stream);
+/* K9 FIXING_FLOAT wire codec (ref src/filter/fixing_float.h:44-95), stochastic rounding */
+int psb_fixfloat_encode_f32(const float* in, int64_t n, int32_t nbytes, double min_v, double max_v,
+                            uint64_t seed, uint8_t* code, void* stream);
+int psb_fixfloat_decode_f32(const uint8_t* code, int64_t n, int32_t nbytes, double min_v, double max_v,
+                            float* out, void* stream);
+int psb_fixfloat_encode_f64(const double* in, int64_t n, int32_t nbytes, double min_v, double max_v,
+                            uint64_t seed, uint8_t* code, void* stream);
+int psb_fixfloat_decode_f64(const uint8_t* code, int64_t n, int32_t nbytes, double min_v, double max_v,
+                            double* out, void* stream);
+/* K19 ParameterInitConfig: type 1 ZERO, 2 CONSTANT, 3 GAUSSIAN (ref shared_array_inl.h:103-130) */
+int psb_fill_f64(double* p, int64_t n, int32_t type, double constant, double mean, double std,
+                 uint64_t seed, void* stream);
+/* K18 popcount of a bitmap; *out_dev zeroed by the caller (ref src/util/bitmap.h:35-75) */
+int psb_bitmap_popcount(const uint32_t* words, int64_t n_words, uint64_t* out_dev, void* stream);
+/* K6/K17 margins of CSR rows with 64-bit keys against a sorted (key, weight) model
+ * (ref src/app/linear_method/model_evaluation.h:40-66) */
+int psb_spmv_lookup(const int64_t* row_ptr, const uint64_t* keys, const float* val, int64_t n_rows,
+                    const uint64_t* dict, const double* w, int64_t n_dict, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -27,7 +27,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr",
     "-Xptxas", "-v", "-I", str(ROOT / "include"),
 ]
-CXX_FLAGS = ["-std=c++17", "-O2", "-g", "-fPIC", "-Wall", "-Wno-sign-compare", "-pthread",
+CXX_FLAGS = ["-std=c++17", "-O2", "-g1", "-fPIC", "-Wall", "-Wno-sign-compare", "-pthread",
              "-I", str(ROOT / "include"), "-I", str(CSRC / "host")]
 
 

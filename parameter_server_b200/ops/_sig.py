@@ -24,6 +24,12 @@ CUDA_SIGS = {
     "psb_compact_csr": "pqppqppppppp", "psb_compact_row_ptr": "pqpqqpp",
     "psb_csr_to_csc": "ppppqqqpppppppp",
     "psb_segments_count": "pqipppp", "psb_segments_fill": "ppqipppp", "psb_key_signature": "pqpp",
+    # eval.cu
+    "psb_auc_exact": "ppqpppppp", "psb_accuracy_logloss": "ppqfpp",
+    "psb_countmin_insert": "ppqpiip", "psb_countmin_query": "pqpiiipp",
+    "psb_fixfloat_encode_f32": "pqiddQpp", "psb_fixfloat_decode_f32": "pqiddpp",
+    "psb_fixfloat_encode_f64": "pqiddQpp", "psb_fixfloat_decode_f64": "pqiddpp",
+    "psb_fill_f64": "pqidddQp", "psb_bitmap_popcount": "pqpp", "psb_spmv_lookup": "pppqppqpp",
     # darlin.cu
     "psb_darlin_pass_begin": "pppp", "psb_darlin_grad_push": "pppiiip",
     "psb_darlin_server_update": "pppiiip", "psb_darlin_pull_update": "pppiiip",
