@@ -298,6 +298,33 @@ int psb_bitmap_popcount(const uint32_t* words, int64_t n_words, uint64_t* out_de
 int psb_spmv_lookup(const int64_t* row_ptr, const uint64_t* keys, const float* val, int64_t n_rows,
                     const uint64_t* dict, const double* w, int64_t n_dict, float* out, void* stream);
 
+
+/* ------------------------------------------------------------------------- *
+ *  Generic sharded KV push / pull over peer memory (kv.cu)
+ *  ref: SharedParameter::push/pull, KVVector::setValue/getValue, sliceKeyOrderedMsg
+ * ------------------------------------------------------------------------- */
+/* (owner, slot) of keys whose dictionary positions are known (idx1 = 1 + position, 0 = unknown);
+ * shard_begin_dev[s] = first dictionary position of server s */
+int psb_kv_route_dense(const uint32_t* idx1, int64_t n, const int64_t* shard_begin_dev,
+                       int32_t n_servers, int32_t* owner, int64_t* slot, void* stream);
+/* push: vals[i] is added into server owner[i]'s array at slot[i] (reductions over NVLink, 128-bit
+ * wide on contiguous runs); pull: the reverse gather.  peers_host[s] = mapping of server s' array */
+int psb_kv_push_add_f32(const float* vals, const int32_t* owner, const int64_t* slot, int64_t n,
+                        float* const* peers_host, int32_t n_servers, void* stream);
+int psb_kv_pull_f32(float* out, const int32_t* owner, const int64_t* slot, int64_t n,
+                    float* const* peers_host, int32_t n_servers, void* stream);
+/* bulk (bandwidth-bound) path: only contiguous value segments cross NVLink; the owner applies /
+ * gathers locally with the slot lists it cached when the handle was registered */
+int psb_kv_bulk_send(const float* src, const int64_t* seg_begin_host, float* const* dst_host,
+                     uint64_t* const* flag_host, int32_t n_servers, uint64_t seq, uint32_t* done_ctr,
+                     void* stream);
+int psb_kv_bulk_apply_add(float* val, const float* landing, const int64_t* slots, int64_t n,
+                          const uint64_t* flag, uint64_t seq, void* stream);
+int psb_kv_bulk_gather_send(const float* val, const int64_t* const* slots_host, const int64_t* count_host,
+                            float* const* dst_host, uint64_t* const* flag_host, int32_t n_workers,
+                            uint64_t seq, uint32_t* done_ctr, void* stream);
+int psb_kv_wait_flags(const uint64_t* flags, int32_t n, uint64_t seq, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -30,6 +30,10 @@ CUDA_SIGS = {
     "psb_fixfloat_encode_f32": "pqiddQpp", "psb_fixfloat_decode_f32": "pqiddpp",
     "psb_fixfloat_encode_f64": "pqiddQpp", "psb_fixfloat_decode_f64": "pqiddpp",
     "psb_fill_f64": "pqidddQp", "psb_bitmap_popcount": "pqpp", "psb_spmv_lookup": "pppqppqpp",
+    # kv.cu
+    "psb_kv_route_dense": "pqpippp", "psb_kv_push_add_f32": "pppqpip", "psb_kv_pull_f32": "pppqpip",
+    "psb_kv_bulk_send": "ppppiQpp", "psb_kv_bulk_apply_add": "pppqpQp",
+    "psb_kv_bulk_gather_send": "pppppiQpp", "psb_kv_wait_flags": "piQp",
     # darlin.cu
     "psb_darlin_pass_begin": "pppp", "psb_darlin_grad_push": "pppiiip",
     "psb_darlin_server_update": "pppiiip", "psb_darlin_pull_update": "pppiiip",

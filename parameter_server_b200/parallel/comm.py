@@ -34,6 +34,10 @@ class Comm:
     def barrier(self) -> None:
         pass
 
+    def alltoall_var(self, parts: list) -> list:
+        """parts[r] goes to rank r; returns what every rank sent to me (set-up time only)."""
+        return list(parts)
+
     def make_arena(self, nbytes: int, device) -> SymmetricArena:
         return SymmetricArena(nbytes, 0, 1, None, device)
 
@@ -77,6 +81,16 @@ class TorchComm(Comm):
     def barrier(self):
         self.dist.barrier(group=self.group)
 
+    def alltoall_var(self, parts):
+        dev, dtype = parts[0].device, parts[0].dtype
+        send = torch.tensor([p.numel() for p in parts], dtype=torch.int64, device=dev)
+        recv = torch.empty_like(send)
+        self.dist.all_to_all_single(recv, send, group=self.group)
+        out_split = recv.tolist()
+        buf = torch.empty(sum(out_split), dtype=dtype, device=dev)
+        self.dist.all_to_all_single(buf, torch.cat(parts), out_split, send.tolist(), group=self.group)
+        return list(torch.split(buf, out_split))
+
     def make_arena(self, nbytes, device):
         return SymmetricArena(nbytes, self.rank, self.world, self.group, device)
 
@@ -115,6 +129,10 @@ class ThreadComm(Comm):
 
     def barrier(self):
         self.sh.bar.wait()
+
+    def alltoall_var(self, parts):
+        everyone = self.gather_obj(parts)
+        return [everyone[r][self.rank] for r in range(self.world)]
 
     def make_arena(self, nbytes, device):
         a = SymmetricArena(nbytes, self.rank, 1, None, device)
