@@ -56,7 +56,7 @@ class SlotReader {
   SArray<uint64> index(int slot_id) {
     SArray<uint64> idx = index_cache_[slot_id];
     if (!idx.empty()) return idx;
-    if (nnzEle(slot_id) == 0) return idx;
+    if (nnzEle(slot_id) == 0 || isDense(slot_id)) return idx;  // dense slots (the label) have no keys
     for (int i = 0; i < data_.file_size(); ++i) {
       SArray<char> comp;
       if (!comp.readFromFile(cacheName(ithFile(data_, i), slot_id) + ".colidx")) continue;
@@ -111,6 +111,10 @@ class SlotReader {
     return readMatrixInfo(info_, slot_id, sizeof(uint64), sizeof(V));
   }
   const ExampleInfo& info() const { return info_; }
+  bool isDense(int slot_id) const {
+    auto it = slot_info_.find(slot_id);
+    return it != slot_info_.end() && it->second.format() == SlotInfoView::DENSE;
+  }
   size_t nnzEle(int slot_id) const {
     auto it = slot_info_.find(slot_id);
     return it == slot_info_.end() ? 0 : (size_t)it->second.nnz_ele();

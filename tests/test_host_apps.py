@@ -154,3 +154,19 @@ def test_async_sgd_variants_learn(dataset, algo, extra):
   async_sgd {{ algo: {algo} {extra} minibatch: 300 num_data_pass: 3 report_interval: 0 tail_feature_freq: 1 }}''')
     loss, auc = map(float, host.run_cluster(conf, 1, 2).split())
     assert loss < 0.66 and auc > 0.75
+
+
+def test_load_slot_data_roundtrip(dataset, tmp_path):
+    """files -> native SlotReader (columnar cache) -> SparseCSR groups"""
+    from parameter_server_b200.utils.data_io import load_slot_data
+    d, shards = dataset
+    conf = f'format: TEXT text: LIBSVM file: "{d}/train/part-0" file: "{d}/train/part-1"'
+    groups = load_slot_data(conf, str(tmp_path / "cache_"))
+    g = groups[1]
+    assert g.n_rows == 2 * ROWS and g.nnz == shards[0].nnz + shards[1].nnz
+    assert torch.equal(g.keys[:shards[0].nnz], shards[0].keys)
+    assert torch.equal(g.y[:ROWS], shards[0].y)
+    assert torch.allclose(g.vals[:shards[0].nnz], shards[0].vals, rtol=1e-5)
+    # second load hits the cache and returns the same arrays
+    g2 = load_slot_data(conf, str(tmp_path / "cache_"))[1]
+    assert torch.equal(g2.keys, g.keys) and torch.equal(g2.row_ptr, g.row_ptr)
