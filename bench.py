@@ -179,6 +179,12 @@ def main() -> None:
         mx = pr[8:8 + 2 * nst]
         p1 = [v >> 20 for v in mx[0::2]]; p3 = [v >> 20 for v in mx[1::2]]
         print('max-over-CTA phase1 us mean %.2f, phase3 %.2f (max over passes); straggler CTAs p1 %s p3 %s' % (sum(p1) / len(p1) / 1e3, sum(p3) / len(p3) / 1e3, collections.Counter(v & 0xfffff for v in mx[0::2]).most_common(4), collections.Counter(v & 0xfffff for v in mx[1::2]).most_common(4)), file=sys.stderr)
+        pc = pr[8 + 2 * nst:8 + 2 * nst + 2 * eng.grid_fused]
+        tot = sorted(((pc[2 * i] / passes / nst / 1e3, i, pc[2 * i + 1]) for i in range(eng.grid_fused)), reverse=True)
+        print('slowest CTAs (mean phase1 us, cta, smid):', [(round(a, 2), b, c) for a, b, c in tot[:12]], 'median', round(tot[len(tot) // 2][0], 2), file=sys.stderr)
+        tp = pr[8 + 2 * nst + 8192:8 + 2 * nst + 8192 + 64]
+        agg = [sum(tp[8 * c + i] for c in range(8)) for i in range(8)]
+        print('warp-0 grad_segment ns: z-load %.0f compute %.0f atomic %.0f | reducer: part-load %.0f update %.0f  (n=%d, reducers=%d)' % (agg[0] / max(agg[5], 1), agg[1] / max(agg[5], 1), agg[2] / max(agg[5], 1), agg[3] / max(agg[6], 1), agg[4] / max(agg[6], 1), agg[5], agg[6]), file=sys.stderr)
         sp = sorted(p1); print('phase1 max-over-CTA quantiles us:', [round(sp[int(q * (len(sp) - 1))] / 1e3, 1) for q in (0, .1, .25, .5, .75, .9, .99, 1)], file=sys.stderr)
         sp = sorted(p3); print('phase3 max-over-CTA quantiles us:', [round(sp[int(q * (len(sp) - 1))] / 1e3, 1) for q in (0, .1, .25, .5, .75, .9, .99, 1)], file=sys.stderr)
         print('per-step us (mean over CTAs):', {n: round(v / eng.grid_fused / passes / nst / 1e3, 2) for n, v in zip(names, pr)}, file=sys.stderr)

@@ -552,158 +552,319 @@ __device__ __forceinline__ double update_coord(const psb_darlin_server& S, const
   return vio;
 }
 
+// Everything about one segment that does not change during a pass, held in registers.  The
+// persistent kernel stages the first segment of every warp for step s+1 while it waits on the
+// last barrier of step s, and keeps it from phase 1 to phase 3 of the step: what remains on the
+// critical path after a barrier is one level of loads of mutable state (margins, trust region,
+// active bit, weights), the arithmetic and the stores.
+struct SegRegs {
+  int64_t v;            // step-local segment number this was staged for (-1: nothing staged)
+  int64_t j, beg, off;  // column, first entry, coordinate offset inside the owner's shard
+  int len, nseg, sc, owner;  // entries; segments of the column; my position among them; owner rank
+  bool first, single;
+  uint32_t idx[kUnroll];
+  float sv[kUnroll];
+};
+
+template <bool BINARY>
+__device__ __forceinline__ void stage_segment(SegRegs& R, const psb_darlin_worker& W,
+                                              const StepPlan& plan, int bps, int64_t v, int lane) {
+  R.v = v;
+  const int q = locate(plan, bps, v);
+  const int64_t s = plan.first[q] + (v - plan.pref[q]);
+  const SegMeta m = load_meta(W.seg_meta, s);
+  R.j = m.j; R.beg = m.beg; R.len = m.len; R.first = m.first; R.single = m.single;
+#pragma unroll
+  for (int k = 0; k < kUnroll; ++k) {
+    const int e = k * 32 + lane;
+    R.idx[k] = e < m.len ? __ldg(W.row_idx + m.beg + e) : 0xffffffffu;
+  }
+  R.owner = __ldg(W.col_owner + m.j);
+  R.off = __ldg(W.col_off + m.j);
+  R.nseg = 1; R.sc = 0;
+  if (!m.single) {
+    const int64_t cs = __ldg(W.col_seg + m.j);
+    R.nseg = (int)(__ldg(W.col_seg + m.j + 1) - cs);
+    R.sc = (int)(s - cs);
+  }
+#pragma unroll
+  for (int k = 0; k < kUnroll; ++k) {
+    const bool ok = R.idx[k] != 0xffffffffu;
+    if (BINARY) R.sv[k] = ok ? __ldg(W.y + R.idx[k]) : 0.f;
+    else R.sv[k] = ok ? __ldg(W.sval + m.beg + k * 32 + lane) : 0.f;
+  }
+}
+
+__device__ __forceinline__ void push_staged(const psb_darlin_worker& W, const SegRegs& R, double g,
+                                            double u) {
+  const int64_t at = (int64_t)W.rank * W.land_cap[R.owner] + R.off;
+  W.land_g[R.owner][at] = g;  // peer store when owner != rank
+  W.land_u[R.owner][at] = u;
+}
+
+// ---- batched fp64 exp / reciprocal ----------------------------------------------------------
+// The gradient needs, per nonzero, tau = 1/(1+e^z) and e^{|x| delta} in double precision.  The
+// library exp() and the IEEE divide are ~30 dependent fp64 operations each and nvcc does not
+// interleave neighbouring calls (measured on B200: 245 cycles per sigmoid at any ILP, DFMA
+// latency 8.3 cycles, benchmarks/micro/fp64_rate.cu), which made this arithmetic the longest
+// item of a step.  Below the same functions are written stage by stage over the kUnroll
+// entries of a batch, so the chains of a batch overlap: table-driven exp (e^x = 2^(k/64) *
+// p(r), |r| <= ln2/128, degree-5 polynomial, error < 1.5 ulp) and a Newton reciprocal seeded
+// by rcp.approx (error < 1 ulp).
+constexpr int kExpTab = 64;
+__device__ __forceinline__ void fill_exp_table(double* tab) {  // tab[j] = 2^(j/64), shared memory
+  for (int j = threadIdx.x; j < kExpTab; j += blockDim.x) tab[j] = exp2((double)j / kExpTab);
+}
+template <int N>
+__device__ __forceinline__ void exp_batch(double (&x)[N], const double* __restrict__ tab) {
+  const double kMagic = 6755399441055744.0;  // 1.5 * 2^52: the integer lands in the low word
+  double kd[N], r[N], p[N];
+  int ki[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) x[i] = fmin(fmax(x[i], -708.0), 708.0);
+#pragma unroll
+  for (int i = 0; i < N; ++i) kd[i] = fma(x[i], 92.33248261689366 /* 64/ln2 */, kMagic);
+#pragma unroll
+  for (int i = 0; i < N; ++i) { ki[i] = __double2loint(kd[i]); kd[i] -= kMagic; }
+#pragma unroll
+  for (int i = 0; i < N; ++i) r[i] = fma(kd[i], -0.01083042469326756 /* ln2/64, low 21 bits clear */, x[i]);
+#pragma unroll
+  for (int i = 0; i < N; ++i) r[i] = fma(kd[i], -2.9815858269852933e-12 /* ln2/64 - hi */, r[i]);
+#pragma unroll
+  for (int i = 0; i < N; ++i) p[i] = fma(r[i], 1.0 / 120, 1.0 / 24);
+#pragma unroll
+  for (int i = 0; i < N; ++i) p[i] = fma(p[i], r[i], 1.0 / 6);
+#pragma unroll
+  for (int i = 0; i < N; ++i) p[i] = fma(p[i], r[i], 0.5);
+#pragma unroll
+  for (int i = 0; i < N; ++i) p[i] = fma(p[i], r[i], 1.0);
+#pragma unroll
+  for (int i = 0; i < N; ++i) p[i] = fma(p[i], r[i], 1.0);
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    const double t = tab[ki[i] & (kExpTab - 1)] * p[i];
+    // scale by 2^(k >> 6): |x| <= 708 keeps the result a normal number
+    x[i] = __hiloint2double(__double2hiint(t) + ((ki[i] >> 6) << 20), __double2loint(t));
+  }
+}
+template <int N>
+__device__ __forceinline__ void rcp_batch(double (&a)[N]) {  // a >= 1
+  double r[N], e[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r[i]) : "d"(a[i]));
+#pragma unroll
+  for (int it = 0; it < 3; ++it) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) e[i] = fma(-a[i], r[i], 1.0);
+#pragma unroll
+    for (int i = 0; i < N; ++i) r[i] = fma(r[i], e[i], r[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < N; ++i) a[i] = r[i];
+}
+
+// time stamp that cannot be hoisted above the value it names (profiling builds of the pass only)
+__device__ __forceinline__ unsigned long long stamp_after(double dep) {
+  unsigned long long t;
+  asm volatile("{ .reg .f64 t; mov.f64 t, %1; mov.u64 %0, %%globaltimer; }" : "=l"(t) : "d"(dep) : "memory");
+  return t;
+}
+
 template <bool BINARY, bool SINGLE>
-__device__ __forceinline__ double grad_phase_packed(const psb_darlin_worker& W, const psb_darlin_server& S,
-                                                    const ServerHyper& h, const StepPlan& plan,
-                                                    int bps, int64_t gw, int64_t nw, int lane) {
-  const int64_t total = plan.pref[bps];
-  double vio_max = 0;
-  for (int64_t v = gw; v < total; v += nw) {
-    const int q = locate(plan, bps, v);
-    const int64_t s = plan.first[q] + (v - plan.pref[q]);
-    const SegMeta m = load_meta(W.seg_meta, s);
-    // one latency level: active word, delta and the first batch of indices/values together
-    const uint32_t aw = __ldcg(W.active + (m.j >> 5));
-    double d = __ldcg(W.delta + m.j);
-    int64_t sk = 0;          // shard coordinate (single-rank: this GPU owns every column)
-    double sw = 0, sdl = 0;  // its weight and trust region, fetched off the critical path
-    uint32_t saw = 0;
-    if (SINGLE) sk = __ldg(W.col_off + m.j);
-    double g = 0, u = 0;
-    for (int base = 0; base < m.len; base += 32 * kUnroll) {
-      uint32_t idx[kUnroll];
-      float sv[kUnroll];
+__device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const psb_darlin_server& S,
+                                               const ServerHyper& h, const SegRegs& R, int lane,
+                                               const double* __restrict__ exp_tab,
+                                               unsigned long long* tp = nullptr) {
+  unsigned long long t0 = 0, t1 = 0, t2 = 0, t3 = 0, t4 = 0;
+  if (tp) t0 = stamp_after(0.0);
+  // one latency level: active word, trust region, the margins and (single rank) the coordinate
+  const uint32_t aw = __ldcg(W.active + (R.j >> 5));
+  double d = __ldcg(W.delta + R.j);
+  double sw = 0, sdl = 0;
+  uint32_t saw = 0;
+  if (SINGLE && lane == 0) {  // any segment may turn out to be the one that reduces the column
+    sw = __ldcg(S.w + R.off);
+    sdl = __ldcg(S.delta + R.off);
+    saw = __ldcg(S.active + (R.off >> 5));
+  }
+  if (!(aw >> (R.j & 31) & 1u)) return 0;  // inactive column: nothing is pushed
+  if (BINARY) d = exp(d);
+  double g = 0, u = 0;
+  uint32_t idx[kUnroll];
+  float sv[kUnroll];
+#pragma unroll
+  for (int k = 0; k < kUnroll; ++k) { idx[k] = R.idx[k]; sv[k] = R.sv[k]; }
+  for (int base = 0; base < R.len; base += 32 * kUnroll) {
+    if (base > 0) {
 #pragma unroll
       for (int k = 0; k < kUnroll; ++k) {
         const int e = base + k * 32 + lane;
-        const bool ok = e < m.len;
-        idx[k] = ok ? __ldg(W.row_idx + m.beg + e) : 0xffffffffu;
-        sv[k] = (ok && !BINARY) ? __ldg(W.sval + m.beg + e) : 0.f;
+        const bool ok = e < R.len;
+        idx[k] = ok ? __ldg(W.row_idx + R.beg + e) : 0xffffffffu;
+        sv[k] = (ok && !BINARY) ? __ldg(W.sval + R.beg + e) : 0.f;
       }
-      if (!(aw >> (m.j & 31) & 1u)) break;  // inactive column: nothing is pushed
-      if (base == 0 && BINARY) d = exp(d);
-      if (SINGLE && base == 0 && lane == 0) {
-        sw = __ldcg(S.w + sk);
-        sdl = __ldcg(S.delta + sk);
-        saw = __ldcg(S.active + (sk >> 5));
-      }
-      double zz[kUnroll];
+      if (BINARY) {
 #pragma unroll
-      for (int k = 0; k < kUnroll; ++k) {
-        zz[k] = idx[k] != 0xffffffffu ? __ldcg(W.z + idx[k]) : 0.0;
-        if (BINARY) sv[k] = idx[k] != 0xffffffffu ? __ldg(W.y + idx[k]) : 0.f;
-      }
-#pragma unroll
-      for (int k = 0; k < kUnroll; ++k) {
-        if (idx[k] == 0xffffffffu) continue;
-        const double tau = 1.0 / (1.0 + exp(zz[k]));
-        const double x = (double)sv[k];
-        if (BINARY) {
-          g -= x * tau;
-          u += fmin(tau * (1.0 - tau) * d, 0.25);
-        } else {
-          g -= tau * x;
-          u += fmin(tau * (1.0 - tau) * exp(fabs(x) * d), 0.25) * x * x;
-        }
+        for (int k = 0; k < kUnroll; ++k) sv[k] = idx[k] != 0xffffffffu ? __ldg(W.y + idx[k]) : 0.f;
       }
     }
-    if (!(aw >> (m.j & 31) & 1u)) continue;
-    g = warp_sum(g);
-    u = warp_sum(u);
-    if (m.single) {
-      if (lane == 0) {
-        if (SINGLE) vio_max = fmax(vio_max, update_coord(S, h, sk, g, u, sw, sdl, saw >> (sk & 31) & 1u));
-        else push_column(W, m.j, g, u);
-      }
-      continue;
+    double zz[kUnroll];
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) zz[k] = idx[k] != 0xffffffffu ? __ldcg(W.z + idx[k]) : 0.0;
+    if (tp && base == 0) t1 = stamp_after(zz[0] + zz[1] + zz[2] + zz[3] + d + sw + sdl);
+    // branch-free over the batch so the four exp/divide chains interleave (fp64 latency bound);
+    // a padding entry has x == 0 and contributes exactly nothing
+    double tau[kUnroll], x[kUnroll], cv[kUnroll];
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) x[k] = (double)sv[k];
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) { tau[k] = zz[k]; cv[k] = BINARY ? d : fabs(x[k]) * d; }
+    exp_batch(tau, exp_tab);
+    if (!BINARY) exp_batch(cv, exp_tab);
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) tau[k] += 1.0;
+    rcp_batch(tau);
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) {
+      g -= tau[k] * x[k];
+      u += fmin(tau[k] * (1.0 - tau[k]) * cv[k], 0.25) * x[k] * x[k];
     }
-    const int64_t cs = W.col_seg[m.j];
-    const int nseg = (int)(W.col_seg[m.j + 1] - cs);
-    int old = 0;
+  }
+  g = warp_sum(g);
+  u = warp_sum(u);
+  if (tp) t2 = stamp_after(g + u);
+  double vio = 0;
+  if (R.single) {
     if (lane == 0) {
-      __stcg(W.part + 2 * v, g);
-      __stcg(W.part + 2 * v + 1, u);
-      // release: the partial is visible before the count; acquire: the last arriver sees all
-      old = (int)atom_add_acqrel_gpu(reinterpret_cast<uint32_t*>(W.col_cnt + m.j), 1u);
+      if (SINGLE) vio = update_coord(S, h, R.off, g, u, sw, sdl, saw >> (R.off & 31) & 1u);
+      else push_staged(W, R, g, u);
     }
-    old = __shfl_sync(FULL, old, 0);
-    if (old == nseg - 1) {
-      const int64_t v0 = v - (s - cs);
-      double sg = 0, su = 0;
-      for (int k = lane; k < nseg; k += 32) {
-        sg += __ldcg(W.part + 2 * (v0 + k));
-        su += __ldcg(W.part + 2 * (v0 + k) + 1);
-      }
-      sg = warp_sum(sg);
-      su = warp_sum(su);
-      if (lane == 0) {
-        if (SINGLE) vio_max = fmax(vio_max, update_coord(S, h, sk, sg, su, sw, sdl, saw >> (sk & 31) & 1u));
-        else push_column(W, m.j, sg, su);
-        W.col_cnt[m.j] = 0;
-      }
+    if (tp && lane == 0) { tp[0] += t1 - t0; tp[1] += t2 - t1; tp[5] += 1; }
+    return vio;
+  }
+  int old = 0;
+  if (lane == 0) {
+    __stcg(W.part + 2 * R.v, g);
+    __stcg(W.part + 2 * R.v + 1, u);
+    // release: the partial is visible before the count; acquire: the last arriver sees all
+    old = (int)atom_add_acqrel_gpu(reinterpret_cast<uint32_t*>(W.col_cnt + R.j), 1u);
+  }
+  old = __shfl_sync(FULL, old, 0);
+  if (tp) t3 = stamp_after((double)old);
+  if (tp && lane == 0) { tp[0] += t1 - t0; tp[1] += t2 - t1; tp[2] += t3 - t2; tp[5] += 1; }
+  if (old == R.nseg - 1) {
+    const int64_t v0 = R.v - R.sc;
+    double sg = 0, su = 0;
+    for (int k = lane; k < R.nseg; k += 32) {  // fixed segment order: bit-reproducible
+      sg += __ldcg(W.part + 2 * (v0 + k));
+      su += __ldcg(W.part + 2 * (v0 + k) + 1);
     }
+    sg = warp_sum(sg);
+    su = warp_sum(su);
+    if (tp) t4 = stamp_after(sg + su);
+    if (lane == 0) {
+      if (SINGLE) vio = update_coord(S, h, R.off, sg, su, sw, sdl, saw >> (R.off & 31) & 1u);
+      else push_staged(W, R, sg, su);
+      W.col_cnt[R.j] = 0;
+    }
+    if (tp && lane == 0) { tp[3] += t4 - t3; tp[4] += stamp_after(vio) - t4; tp[6] += 1; }
+  }
+  return vio;
+}
+
+template <bool BINARY, bool SINGLE>
+__device__ __forceinline__ double grad_phase_packed(const psb_darlin_worker& W, const psb_darlin_server& S,
+                                                    const ServerHyper& h, const StepPlan& plan,
+                                                    int bps, int64_t gw, int64_t nw, int lane,
+                                                    const SegRegs& pre, const double* __restrict__ exp_tab,
+                                                    unsigned long long* tp = nullptr) {
+  const int64_t total = plan.pref[bps];
+  double vio_max = 0;
+  if (gw < total) {
+    if (pre.v == gw) {
+      vio_max = grad_segment<BINARY, SINGLE>(W, S, h, pre, lane, exp_tab, tp);
+    } else {
+      SegRegs R;
+      stage_segment<BINARY>(R, W, plan, bps, gw, lane);
+      vio_max = grad_segment<BINARY, SINGLE>(W, S, h, R, lane, exp_tab);
+    }
+  }
+  for (int64_t v = gw + nw; v < total; v += nw) {
+    SegRegs R;
+    stage_segment<BINARY>(R, W, plan, bps, v, lane);
+    vio_max = fmax(vio_max, grad_segment<BINARY, SINGLE>(W, S, h, R, lane, exp_tab));
   }
   return vio_max;
 }
 
 template <bool BINARY>
-__device__ __forceinline__ void pull_phase_packed(const psb_darlin_worker& W, const StepPlan& plan,
-                                                  int bps, double delta_max, int64_t gw, int64_t nw,
-                                                  int lane) {
-  const int64_t total = plan.pref[bps];
-  for (int64_t v = gw; v < total; v += nw) {
-    const int q = locate(plan, bps, v);
-    const int64_t s = plan.first[q] + (v - plan.pref[q]);
-    const SegMeta m = load_meta(W.seg_meta, s);
-    const int o = __ldg(W.col_owner + m.j);
-    const int64_t off = __ldg(W.col_off + m.j);
-    const uint32_t aw = __ldcg(W.active + (m.j >> 5));
-    double w_new = 0, d = 0;
-    if (lane == 0) {
-      w_new = ld_volatile_f64(W.srv_w[o] + off);  // peer load when o != rank
-      d = ld_volatile_f64(W.srv_dw[o] + off);
+__device__ __forceinline__ void pull_segment(const psb_darlin_worker& W, const SegRegs& R,
+                                             double delta_max, int lane) {
+  const uint32_t aw = __ldcg(W.active + (R.j >> 5));
+  double w_new = 0, d = 0;
+  if (lane == 0) {
+    w_new = ld_volatile_f64(W.srv_w[R.owner] + R.off);  // peer load when owner != rank
+    d = ld_volatile_f64(W.srv_dw[R.owner] + R.off);
+  }
+  w_new = __shfl_sync(FULL, w_new, 0);
+  d = __shfl_sync(FULL, d, 0);
+  if (is_marked(w_new)) {  // the server filtered this coordinate (ref darlin.h:439-444)
+    if (R.first && lane == 0) {
+      bit_clear_atomic(W.active, R.j);
+      W.w[R.j] = 0;
     }
-    uint32_t idx[kUnroll];
-    float sv[kUnroll];
+    return;
+  }
+  if (!(aw >> (R.j & 31) & 1u)) return;
+  if (R.first && lane == 0) {
+    W.w[R.j] = w_new;
+    W.delta[R.j] = fmin(delta_max, 2 * fabs(d) + .1);
+  }
+  if (d == 0) return;
+  uint32_t idx[kUnroll];
+  float sv[kUnroll];
 #pragma unroll
-    for (int k = 0; k < kUnroll; ++k) {  // speculative first batch, overlaps the w/dw round trip
-      const int e = k * 32 + lane;
-      const bool ok = e < m.len;
-      idx[k] = ok ? __ldg(W.row_idx + m.beg + e) : 0xffffffffu;
-      sv[k] = (ok && !BINARY) ? __ldg(W.sval + m.beg + e) : 0.f;
-    }
-    w_new = __shfl_sync(FULL, w_new, 0);
-    d = __shfl_sync(FULL, d, 0);
-    if (is_marked(w_new)) {  // the server filtered this coordinate (ref darlin.h:439-444)
-      if (m.first && lane == 0) {
-        bit_clear_atomic(W.active, m.j);
-        W.w[m.j] = 0;
-      }
-      continue;
-    }
-    if (!(aw >> (m.j & 31) & 1u)) continue;
-    if (m.first && lane == 0) {
-      W.w[m.j] = w_new;
-      W.delta[m.j] = fmin(delta_max, 2 * fabs(d) + .1);
-    }
-    if (d == 0) continue;
-    for (int base = 0; base < m.len; base += 32 * kUnroll) {
-      if (base > 0) {
-#pragma unroll
-        for (int k = 0; k < kUnroll; ++k) {
-          const int e = base + k * 32 + lane;
-          const bool ok = e < m.len;
-          idx[k] = ok ? __ldg(W.row_idx + m.beg + e) : 0xffffffffu;
-          sv[k] = (ok && !BINARY) ? __ldg(W.sval + m.beg + e) : 0.f;
-        }
-      }
+  for (int k = 0; k < kUnroll; ++k) { idx[k] = R.idx[k]; sv[k] = R.sv[k]; }
+  for (int base = 0; base < R.len; base += 32 * kUnroll) {
+    if (base > 0) {
 #pragma unroll
       for (int k = 0; k < kUnroll; ++k) {
-        if (idx[k] == 0xffffffffu) continue;
-        const double x = BINARY ? (double)__ldg(W.y + idx[k]) : (double)sv[k];
-        atomicAdd(W.z + idx[k], d * x);  // dual_i *= exp(y_i d x_ij)  <=>  z_i += d * sval
+        const int e = base + k * 32 + lane;
+        const bool ok = e < R.len;
+        idx[k] = ok ? __ldg(W.row_idx + R.beg + e) : 0xffffffffu;
+        sv[k] = (ok && !BINARY) ? __ldg(W.sval + R.beg + e) : 0.f;
+      }
+      if (BINARY) {
+#pragma unroll
+        for (int k = 0; k < kUnroll; ++k) sv[k] = idx[k] != 0xffffffffu ? __ldg(W.y + idx[k]) : 0.f;
       }
     }
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) {
+      if (idx[k] == 0xffffffffu) continue;
+      atomicAdd(W.z + idx[k], d * (double)sv[k]);  // dual_i *= exp(y_i d x_ij)  <=>  z_i += d * sval
+    }
+  }
+}
+
+template <bool BINARY>
+__device__ __forceinline__ void pull_phase_packed(const psb_darlin_worker& W, const StepPlan& plan,
+                                                  int bps, double delta_max, int64_t gw, int64_t nw,
+                                                  int lane, const SegRegs& pre) {
+  const int64_t total = plan.pref[bps];
+  if (gw < total) {
+    if (pre.v == gw) {
+      pull_segment<BINARY>(W, pre, delta_max, lane);
+    } else {
+      SegRegs R;
+      stage_segment<BINARY>(R, W, plan, bps, gw, lane);
+      pull_segment<BINARY>(W, R, delta_max, lane);
+    }
+  }
+  for (int64_t v = gw + nw; v < total; v += nw) {
+    SegRegs R;
+    stage_segment<BINARY>(R, W, plan, bps, v, lane);
+    pull_segment<BINARY>(W, R, delta_max, lane);
   }
 }
 
@@ -790,6 +951,8 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
   __shared__ FusedPlan plans[2];
   __shared__ double sh[4][kWarps];
   __shared__ bool s_last;
+  __shared__ double exp_tab[kExpTab];
+  fill_exp_table(exp_tab);
   // optional per-phase time accounting (thread 0 of every CTA, summed into prof[0..4])
   unsigned long long t_mark = 0, t_acc[5] = {0, 0, 0, 0, 0};
 #define PSB_PROF(slot)                                         \
@@ -801,9 +964,14 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
   }
   if (prof && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_mark));
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int64_t gw = (int64_t)blockIdx.x * kWarps + wid, nw = (int64_t)gridDim.x * kWarps;
-  const int64_t gt = (int64_t)blockIdx.x * kThreads + threadIdx.x, nt = (int64_t)gridDim.x * kThreads;
   const uint32_t G = gridDim.x;
+  // segment v of a step goes to CTA v % G (warp v / G): a step with fewer segments than warps
+  // is spread over every SM instead of filling the first CTAs
+  const int64_t gw = (ctrl->flags & 4) ? (int64_t)blockIdx.x * kWarps + wid : (int64_t)wid * G + blockIdx.x;
+  const int64_t nw = (int64_t)G * kWarps;
+  const int64_t gt = (int64_t)blockIdx.x * kThreads + threadIdx.x, nt = (int64_t)gridDim.x * kThreads;
+  SegRegs pre;
+  pre.v = -1;
   uint32_t nbar = 0;
   const bool multi = W.n_workers > 1;
   const ServerHyper h{ctrl->lambda, ctrl->eta, ctrl->delta_max, ctrl->kkt_threshold};
@@ -828,6 +996,7 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
   }
   if (wid == 0 && n_steps > 0) fused_plan(plans[0], blk_tab, order, 0, bps);
   grid_arrive(bar + 3);
+  if (n_steps > 0 && gw < plans[0].wk.pref[bps]) stage_segment<BINARY>(pre, W, plans[0].wk, bps, gw, lane);
   grid_wait(bar + 3, ++nbar * G);
 
   for (int step = 0; step < n_steps; ++step) {
@@ -838,14 +1007,20 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
     const bool has_next = step + 1 < n_steps;
     // ---- phase 1: gradient + push ----
     {
-      const int64_t gwr = (ctrl->flags & 2) ? (gw + (int64_t)step * 8 * 37) % nw : gw;  // experiment
-      const double vio = grad_phase_packed<BINARY, SINGLE>(W, S, h, P.wk, bps, gwr, nw, lane);
+      unsigned long long* tp = (prof && wid == 0) ? prof + 8 + 2 * (unsigned long long)n_steps + 2 * 4096 + 8 * (blockIdx.x & 7) : nullptr;
+      const double vio = grad_phase_packed<BINARY, SINGLE>(W, S, h, P.wk, bps, gw, nw, lane, pre, exp_tab, tp);
       if (SINGLE && vio > 0) atomic_max_nonneg(S.violation, vio);
     }
     if (prof && threadIdx.x == 0) {  // per-step straggler: max phase-1 time and its CTA
       unsigned long long now_;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
       atomicMax(prof + 8 + 2 * step, ((now_ - t_mark) << 20) | blockIdx.x);
+      // per-CTA totals behind the per-step records: [sum of phase-1 ns, smid]
+      unsigned smid_;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid_));
+      unsigned long long* per_cta = prof + 8 + 2 * (unsigned long long)n_steps + 2 * blockIdx.x;
+      per_cta[0] += now_ - t_mark;
+      per_cta[1] = smid_;
     }
     PSB_PROF(0)
     if (SINGLE) {
@@ -858,7 +1033,7 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
       PSB_PROF(1)
       grid_wait(bar, (uint32_t)(step + 1) * G);
       PSB_PROF(2)
-      pull_phase_packed<BINARY>(W, P.wk, bps, h.delta_max, gw, nw, lane);
+      pull_phase_packed<BINARY>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre);
       if (prof && threadIdx.x == 0) {
         unsigned long long now_;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
@@ -866,6 +1041,8 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
       }
       PSB_PROF(3)
       grid_arrive(bar + 2);
+      pre.v = -1;
+      if (has_next && gw < Pn.wk.pref[bps]) stage_segment<BINARY>(pre, W, Pn.wk, bps, gw, lane);
       grid_wait(bar + 2, (uint32_t)(step + 1) * G);
       PSB_PROF(4)
       continue;
@@ -936,9 +1113,11 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
       __syncthreads();
     }
     PSB_PROF(2)
-    pull_phase_packed<BINARY>(W, P.wk, bps, h.delta_max, gw, nw, lane);
+    pull_phase_packed<BINARY>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre);
     PSB_PROF(3)
     grid_arrive(bar + 2);
+    pre.v = -1;
+    if (has_next && gw < Pn.wk.pref[bps]) stage_segment<BINARY>(pre, W, Pn.wk, bps, gw, lane);
     grid_wait(bar + 2, (uint32_t)(step + 1) * G);
     PSB_PROF(4)
   }

@@ -329,7 +329,7 @@ class DarlinEngine:
         if cfg.fused_grid > 0:
             self.grid_fused = min(self.grid_fused, cfg.fused_grid)
         self.bar = torch.zeros(4, dtype=torch.int32, device=dev)
-        self.prof = torch.zeros(8 + 2 * (len(self.blocks) + len(self.prior_blk_order) + 2), dtype=torch.int64, device=dev)
+        self.prof = torch.zeros(8 + 2 * (len(self.blocks) + len(self.prior_blk_order) + 2) + 2 * 4096 + 64, dtype=torch.int64, device=dev)
         self.eval_scratch = torch.zeros(
             K.evaluate_scratch_bytes(max(self.grid_eval, 4 * sm)) // 8 + 2, **f64)
         # host-pinned staging for the per-pass inputs / result
