@@ -797,14 +797,20 @@ __device__ __forceinline__ double grad_phase_packed(const psb_darlin_worker& W, 
   return vio_max;
 }
 
-template <bool BINARY>
+template <bool BINARY, bool MIRROR>
 __device__ __forceinline__ void pull_segment(const psb_darlin_worker& W, const SegRegs& R,
                                              double delta_max, int lane) {
   const uint32_t aw = __ldcg(W.active + (R.j >> 5));
   double w_new = 0, d = 0;
   if (lane == 0) {
-    w_new = ld_volatile_f64(W.srv_w[R.owner] + R.off);  // peer load when owner != rank
-    d = ld_volatile_f64(W.srv_dw[R.owner] + R.off);
+    if (MIRROR) {  // stored here by the owner before it raised the version flag
+      const int64_t at = (int64_t)R.owner * W.mir_cap + R.off;
+      w_new = ld_volatile_f64(W.mir_w + at);
+      d = ld_volatile_f64(W.mir_dw + at);
+    } else {
+      w_new = ld_volatile_f64(W.srv_w[R.owner] + R.off);
+      d = ld_volatile_f64(W.srv_dw[R.owner] + R.off);
+    }
   }
   w_new = __shfl_sync(FULL, w_new, 0);
   d = __shfl_sync(FULL, d, 0);
@@ -847,24 +853,24 @@ __device__ __forceinline__ void pull_segment(const psb_darlin_worker& W, const S
   }
 }
 
-template <bool BINARY>
+template <bool BINARY, bool MIRROR>
 __device__ __forceinline__ void pull_phase_packed(const psb_darlin_worker& W, const StepPlan& plan,
                                                   int bps, double delta_max, int64_t gw, int64_t nw,
                                                   int lane, const SegRegs& pre) {
   const int64_t total = plan.pref[bps];
   if (gw < total) {
     if (pre.v == gw) {
-      pull_segment<BINARY>(W, pre, delta_max, lane);
+      pull_segment<BINARY, MIRROR>(W, pre, delta_max, lane);
     } else {
       SegRegs R;
       stage_segment<BINARY>(R, W, plan, bps, gw, lane);
-      pull_segment<BINARY>(W, R, delta_max, lane);
+      pull_segment<BINARY, MIRROR>(W, R, delta_max, lane);
     }
   }
   for (int64_t v = gw + nw; v < total; v += nw) {
     SegRegs R;
     stage_segment<BINARY>(R, W, plan, bps, v, lane);
-    pull_segment<BINARY>(W, R, delta_max, lane);
+    pull_segment<BINARY, MIRROR>(W, R, delta_max, lane);
   }
 }
 
@@ -917,6 +923,103 @@ __device__ __forceinline__ double server_phase_ilp(const psb_darlin_server& S, c
   return vio_max;
 }
 
+// ---- fused multi-rank pass: landing slots that are their own arrival flags --------------------
+// A worker's push is two plain 8-byte peer stores (g, u).  The server thread of a coordinate
+// polls the slots of the workers that hold the column (S.has) until neither is the EMPTY
+// pattern, stores EMPTY back, reduces in worker order (bit-reproducible), applies the proximal
+// update and stores (w, dw) into every such worker's mirror.  No ticket, no push flag, no
+// system fence on the push side: the NVLink flight of the pushes overlaps the local grid
+// barrier that separates the margin reads of phase 1 from the margin updates of phase 3.
+// A slot is written at most once per visit of its block, and two visits are separated by
+// grid barriers on both sides, so the stored-back EMPTY is in L2 long before the next push.
+constexpr unsigned long long kEmptySlot = PSB_DARLIN_EMPTY_SLOT;
+constexpr uint32_t kSpinLimit = 1u << 26;  // ~10 s of polling: trap instead of hanging the GPU
+
+__device__ __forceinline__ double poll_slot(double* slot) {
+  unsigned long long bits;
+  uint32_t spins = 0;
+  while ((bits = *reinterpret_cast<volatile unsigned long long*>(slot)) == kEmptySlot) {
+    if (++spins > kSpinLimit) __trap();
+  }
+  return __longlong_as_double((long long)bits);
+}
+
+__device__ __forceinline__ double server_phase_direct(const psb_darlin_server& S, const ServerHyper& h,
+                                                      const StepPlan& plan, int bps, int64_t tid,
+                                                      int64_t nthreads) {
+  const int64_t total = plan.pref[bps];
+  double vio_max = 0;
+  for (int64_t v = tid; v < total; v += nthreads) {
+    const int q = locate(plan, bps, v);
+    const int64_t k = plan.first[q] + (v - plan.pref[q]);
+    const uint32_t aw = __ldcg(S.active + (k >> 5));
+    const double w = __ldcg(S.w + k);
+    const double dl = __ldcg(S.delta + k);
+    const uint32_t has = __ldg(S.has + k);
+    // a worker pushes exactly when its copy of the active bit is set, and the two copies
+    // change together (the mark published below clears the workers' bits in their phase 3)
+    if (!(aw >> (k & 31) & 1u)) continue;
+    double g = 0, u = 0;
+    for (int r = 0; r < S.n_workers; ++r) {
+      if (!(has >> r & 1u)) continue;
+      const int64_t at = (int64_t)r * S.land_cap + k;
+      g += poll_slot(S.land_g + at);
+      u += poll_slot(S.land_u + at);
+      *reinterpret_cast<unsigned long long*>(S.land_g + at) = kEmptySlot;
+      *reinterpret_cast<unsigned long long*>(S.land_u + at) = kEmptySlot;
+    }
+    if (is_marked(w)) {  // filtered earlier and not revived: keep both bit copies clear
+      bit_clear_atomic(S.active, k);
+      continue;
+    }
+    u = u / h.eta + 1e-10;
+    const double g_pos = g + h.lambda, g_neg = g - h.lambda;
+    double d = -w, vio = 0, w_new, dw;
+    bool filtered = false;
+    if (w == 0) {
+      if (g_pos < 0) {
+        vio = -g_pos;
+      } else if (g_neg > 0) {
+        vio = g_neg;
+      } else if (g_pos > h.thr && g_neg < -h.thr) {
+        filtered = true;
+      }
+    }
+    if (filtered) {
+      bit_clear_atomic(S.active, k);
+      w_new = nan_mark();
+      dw = 0;
+    } else {
+      vio_max = fmax(vio_max, vio);
+      if (g_pos <= u * w) {
+        d = -g_pos / u;
+      } else if (g_neg >= u * w) {
+        d = -g_neg / u;
+      }
+      d = fmin(dl, fmax(-dl, d));
+      S.delta[k] = fmin(h.delta_max, 2 * fabs(d) + .1);
+      w_new = w + d;
+      dw = w_new - w;
+    }
+    S.w[k] = w_new;
+    S.dw[k] = dw;
+    for (int r = 0; r < S.n_workers; ++r) {
+      if (!(has >> r & 1u)) continue;
+      S.mir_w[r][k] = w_new;  // peer store when r != rank
+      S.mir_dw[r][k] = dw;
+    }
+  }
+  return vio_max;
+}
+
+__device__ __forceinline__ void spin_flag_ge(const uint64_t* flag, uint64_t want) {
+  uint32_t spins = 0;
+  while (ld_acquire_sys(flag) < want) {
+    __nanosleep(20);
+    if (++spins > kSpinLimit) __trap();
+  }
+}
+
 __device__ __forceinline__ void prefetch_l2(const void* p) {
   asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }
@@ -950,7 +1053,6 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
               double* scratch, unsigned long long* prof) {
   __shared__ FusedPlan plans[2];
   __shared__ double sh[4][kWarps];
-  __shared__ bool s_last;
   __shared__ double exp_tab[kExpTab];
   fill_exp_table(exp_tab);
   // optional per-phase time accounting (thread 0 of every CTA, summed into prof[0..4])
@@ -973,7 +1075,6 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
   SegRegs pre;
   pre.v = -1;
   uint32_t nbar = 0;
-  const bool multi = W.n_workers > 1;
   const ServerHyper h{ctrl->lambda, ctrl->eta, ctrl->delta_max, ctrl->kkt_threshold};
   const uint64_t seq_base = ctrl->seq_base;
   const bool do_prefetch = !(ctrl->flags & 1);
@@ -1033,7 +1134,7 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
       PSB_PROF(1)
       grid_wait(bar, (uint32_t)(step + 1) * G);
       PSB_PROF(2)
-      pull_phase_packed<BINARY>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre);
+      pull_phase_packed<BINARY, false>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre);
       if (prof && threadIdx.x == 0) {
         unsigned long long now_;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
@@ -1047,73 +1148,50 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
       PSB_PROF(4)
       continue;
     }
-    __syncthreads();
-    if (threadIdx.x == 0)
-      s_last = atom_add_acqrel_gpu(bar, 1u) == (uint32_t)(step + 1) * G - 1u;
+    // ---- more than one rank ----
+    // barrier A (local): every margin read of phase 1 precedes every margin update of phase 3.
+    // The pushes are already in flight; the shard update runs between arrive and wait.
+    grid_arrive(bar);
     if (wid == 0 && has_next) fused_plan(plans[(step + 1) & 1], blk_tab, order, step + 1, bps);
-    __syncthreads();
     if (nkeys <= single_cta_keys) {
-      // ---- phase 2, small step: the CTA that finished phase 1 last updates the shard at once,
-      //      everybody else warms L2 for the next step and waits for its stamp ----
-      if (s_last) {
-        if (multi) {
-          if (threadIdx.x < W.n_servers && threadIdx.x != W.rank && (P.wk.mask >> threadIdx.x & 1u)) {
-            __threadfence_system();
-            st_release_sys(W.push_flag[threadIdx.x] + W.rank, seq);
-          }
-          if (nkeys > 0 && threadIdx.x < S.n_workers && threadIdx.x != S.rank)
-            spin_until_ge(S.push_flag + threadIdx.x, seq);
-          __syncthreads();
-        }
-        if (nkeys > 0) {
-          double vio = server_phase_ilp(S, h, P.sv, bps, threadIdx.x, kThreads);
-          vio = warp_max(vio);
-          if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
-          __syncthreads();
-          if (multi && threadIdx.x < S.n_workers && threadIdx.x != S.rank) {
-            __threadfence_system();
-            st_release_sys(S.ver_flag[threadIdx.x], seq);
-          }
-        }
+      // small step: one CTA (the one with the fewest segments) serves the shard
+      if (blockIdx.x == G - 1 && nkeys > 0) {
+        double vio = server_phase_direct(S, h, P.sv, bps, threadIdx.x, kThreads);
+        vio = warp_max(vio);
+        if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
         __syncthreads();
-        if (threadIdx.x == 0) st_release_gpu(bar + 1, (uint32_t)(step + 1));
-      } else {
-        if (has_next && do_prefetch) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
-        if (threadIdx.x == 0) spin_gpu_ge(bar + 1, (uint32_t)(step + 1));
+        if (threadIdx.x < S.n_workers) {  // mirrors first, then the version (own rank included)
+          __threadfence_system();
+          st_release_sys(S.ver_flag[threadIdx.x], seq);
+        }
       }
       __syncthreads();
-    } else {
-      // ---- phase 2, large step: all CTAs share the coordinates between two grid barriers ----
+      if (has_next && do_prefetch) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
+      PSB_PROF(1)
       grid_wait(bar, (uint32_t)(step + 1) * G);
-      if (multi && blockIdx.x == G - 1 && threadIdx.x < W.n_servers && threadIdx.x != W.rank &&
-          (P.wk.mask >> threadIdx.x & 1u)) {
-        __threadfence_system();
-        st_release_sys(W.push_flag[threadIdx.x] + W.rank, seq);
-      }
-      if (multi) {
-        if (threadIdx.x < S.n_workers && threadIdx.x != S.rank)
-          spin_until_ge(S.push_flag + threadIdx.x, seq);
-        __syncthreads();
-      }
-      double vio = server_phase_ilp(S, h, P.sv, bps, gt, nt);
+    } else {
+      // large step: all CTAs share the coordinates, one more grid barrier before the flags
+      __syncthreads();
+      PSB_PROF(1)
+      grid_wait(bar, (uint32_t)(step + 1) * G);
+      double vio = server_phase_direct(S, h, P.sv, bps, gt, nt);
       vio = warp_max(vio);
       if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
       grid_arrive(bar + 3);
       grid_wait(bar + 3, ++nbar * G);
-      if (multi && blockIdx.x == G - 1 && threadIdx.x < S.n_workers && threadIdx.x != S.rank) {
+      if (blockIdx.x == G - 1 && threadIdx.x < S.n_workers) {
         __threadfence_system();
         st_release_sys(S.ver_flag[threadIdx.x], seq);
       }
-      if (threadIdx.x == 0 && blockIdx.x == 0) st_release_gpu(bar + 1, (uint32_t)(step + 1));
     }
-    // ---- phase 3: pull + margin update ----
-    if (multi && P.wk.pref[bps] > 0) {
-      if (threadIdx.x < W.n_servers && threadIdx.x != W.rank && (P.wk.mask >> threadIdx.x & 1u))
-        spin_until_ge(W.ver_flag + threadIdx.x, seq);
+    // ---- phase 3: wait for the owners' versions, then pull from the local mirror ----
+    if (P.wk.pref[bps] > 0) {
+      if (threadIdx.x < W.n_servers && (P.wk.mask >> threadIdx.x & 1u))
+        spin_flag_ge(W.ver_flag + threadIdx.x, seq);
       __syncthreads();
     }
     PSB_PROF(2)
-    pull_phase_packed<BINARY>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre);
+    pull_phase_packed<BINARY, true>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre);
     PSB_PROF(3)
     grid_arrive(bar + 2);
     pre.v = -1;
@@ -1300,6 +1378,10 @@ PSB_API int psb_darlin_fused_pass(const psb_darlin_worker* wk, const psb_darlin_
                   (void*)&bps, (void*)&bar, (void*)&out_local, (void*)&out_peer, (void*)&np,
                   (void*)&scratch, (void*)&prof};
   const bool single = wk->n_workers == 1 && wk->n_servers == 1;
+  if (!single)
+    PSB_REQUIRE(wk->mir_w && wk->mir_dw && wk->mir_cap > 0 && sv->has && sv->mir_w[0] && sv->mir_dw[0],
+                "psb_darlin_fused_pass: the multi-rank pass needs the mirrors and the holder masks "
+                "(worker.mir_*, server.mir_*, server.has) and EMPTY-filled landing slots");
   const void* fn = wk->sval
       ? (single ? (const void*)k_darlin_pass<false, true> : (const void*)k_darlin_pass<false, false>)
       : (single ? (const void*)k_darlin_pass<true, true> : (const void*)k_darlin_pass<true, false>);

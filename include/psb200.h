@@ -90,6 +90,11 @@ typedef struct psb_darlin_worker {
   const uint64_t* ver_flag;           /* local: [n_servers], written by the servers */
   const void* seg_meta;               /* [n_seg] int4 {col, len | first<<16 | single<<17, beg lo,
                                          beg hi}: one 16-byte load per segment (fused kernel) */
+  /* fused multi-rank pass: the servers store every updated coordinate into this worker's own
+   * mirror (index owner*mir_cap + col_off) before raising ver_flag, so the pull is local */
+  const double* mir_w;
+  const double* mir_dw;
+  int64_t mir_cap;
 } psb_darlin_worker;
 
 /* Server side: one key-range shard of the model. */
@@ -108,7 +113,16 @@ typedef struct psb_darlin_server {
   int64_t n_keys;
   int32_t rank, n_workers, n_servers;
   uint64_t* ver_flag[PSB_MAX_PEERS];  /* on worker r: &ver_flag_r[rank] */
+  /* fused multi-rank pass */
+  double* mir_w[PSB_MAX_PEERS];       /* on worker r: &mir_w_r[rank*mir_cap] */
+  double* mir_dw[PSB_MAX_PEERS];
+  const uint32_t* has;                /* [n_keys] bit r set: worker r holds nonzeros of the key */
 } psb_darlin_server;
+
+/* Bit pattern of an empty landing slot in the fused multi-rank pass (a quiet NaN that no
+ * arithmetic produces).  A worker's push overwrites it; the server polls for "not empty",
+ * consumes the value and stores the pattern back: the data is its own arrival flag. */
+#define PSB_DARLIN_EMPTY_SLOT 0x7ff8dead5107e001ull
 
 /* Pass begin: violation=0 and, if ctrl->reset_kkt_filter, refill the active sets.
  * Either struct pointer may be NULL. ref: darlin.h:176-182,297-300 */

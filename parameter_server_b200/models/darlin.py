@@ -297,13 +297,16 @@ class DarlinEngine:
         cap = max(max(self.shard_len), 1)
         self.land_cap = cap
         self.bps = max(1, min(cfg.max_block_delay + 1, 32))
-        nbytes = (2 * W * cap + 2 * cap) * 8 + (2 * W + 4 * W) * 8 + W * 48 + 64 * 256
+        nbytes = (2 * W * cap + 2 * cap + 2 * W * cap) * 8 + (2 * W + 4 * W) * 8 + W * 48 + 64 * 256
         self.arena = self.comm.make_arena(nbytes, dev)
         A = self.arena
         self.b_land_g = A.alloc("land_g", W * cap, torch.float64)
         self.b_land_u = A.alloc("land_u", W * cap, torch.float64)
         self.b_w = A.alloc("w", cap, torch.float64)
         self.b_dw = A.alloc("dw", cap, torch.float64)
+        # fused multi-rank pass: mirrors of every shard, written by the owners (psb200.h)
+        self.b_mir_w = A.alloc("mir_w", W * cap, torch.float64)
+        self.b_mir_dw = A.alloc("mir_dw", W * cap, torch.float64)
         self.b_push_flag = A.alloc("push_flag", W, torch.int64)
         self.b_ver_flag = A.alloc("ver_flag", W, torch.int64)
         self.b_bar_flag = A.alloc("bar_flag", W, torch.int64)
@@ -363,6 +366,7 @@ class DarlinEngine:
             wk.srv_dw[s] = A.peer_ptr(s, self.b_dw)
         wk.ver_flag = self.b_ver_flag.ptr
         wk.seg_meta = self.seg_meta.data_ptr()
+        wk.mir_w, wk.mir_dw, wk.mir_cap = self.b_mir_w.ptr, self.b_mir_dw.ptr, cap
         self.wk = wk
 
         sv = K.DarlinServer()
@@ -374,6 +378,15 @@ class DarlinEngine:
         sv.n_keys, sv.rank, sv.n_workers, sv.n_servers = n_keys, self.rank, W, W
         for r in range(W):
             sv.ver_flag[r] = A.peer_ptr(r, self.b_ver_flag, self.rank)
+            sv.mir_w[r] = A.peer_ptr(r, self.b_mir_w, self.rank * cap)
+            sv.mir_dw[r] = A.peer_ptr(r, self.b_mir_dw, self.rank * cap)
+        self.srv_has = self._holder_masks()
+        sv.has = self.srv_has.data_ptr()
+        self.direct_landing = bool(cfg.fused and W > 1 and self.grid_fused > 0)
+        if self.direct_landing:  # slots are their own arrival flags (PSB_DARLIN_EMPTY_SLOT)
+            empty = torch.tensor([K.EMPTY_SLOT], dtype=torch.int64, device=dev)
+            self.b_land_g.tensor.view(torch.int64).copy_(empty.expand(W * cap))
+            self.b_land_u.tensor.view(torch.int64).copy_(empty.expand(W * cap))
         self.sv = sv
         self.prog_peer = torch.tensor([A.peer_ptr(r, self.b_progress, 6 * self.rank)
                                        for r in range(W)], dtype=torch.int64, device=dev)
@@ -381,6 +394,23 @@ class DarlinEngine:
         self._warm_kernels()
         torch.cuda.synchronize(dev)
         self.comm.barrier()
+
+    def _holder_masks(self) -> torch.Tensor:
+        """has[k] bit r: worker r holds nonzeros of shard key k (it pushes that key every time
+        the key is active).  Set-up time exchange: one byte per (worker, column)."""
+        dev, W = self.device, self.world
+        present = (self.col_ptr[1:] > self.col_ptr[:-1]).to(torch.uint8)
+        parts = []
+        for s in range(W):
+            cols = (self.col_owner == s).nonzero().flatten()
+            dense = torch.zeros(self.shard_len[s], dtype=torch.uint8, device=dev)
+            dense[self.col_off[cols]] = present[cols]
+            parts.append(dense)
+        got = self.comm.alltoall_var(parts)
+        has = torch.zeros(max(self.shard_len[self.rank], 1), dtype=torch.int32, device=dev)
+        for r in range(W):
+            has[:got[r].numel()] |= got[r].to(torch.int32) << r
+        return has
 
     def _warm_kernels(self) -> None:
         """Load every kernel once with an empty step so that graph capture never triggers a
@@ -398,8 +428,19 @@ class DarlinEngine:
     # ----------------------------------------------------------------------------------------
     # one pass
     # ----------------------------------------------------------------------------------------
+    def use_split_protocol(self) -> None:
+        """Switch the landing slots to the flag protocol of the split kernels (zero-filled,
+        push flags).  Used by the lock-step emulation, which cannot run the persistent kernel
+        of several ranks on one GPU."""
+        if self.direct_landing:
+            self.b_land_g.tensor.zero_()
+            self.b_land_u.tensor.zero_()
+            self.direct_landing = False
+
     def _enqueue(self, n_steps: int) -> None:
         if self.cfg.fused and self.grid_fused > 0:
+            if self.world > 1 and not self.direct_landing:
+                raise RuntimeError("this engine was switched to the split-kernel landing protocol")
             K.fused_pass(self.wk, self.sv, self.ctrl_dev.data_ptr(), self.order_dev.data_ptr(),
                          self.blk_tab.data_ptr(), n_steps, self.bps, self.grid_fused,
                          self.bar.data_ptr(),
@@ -407,6 +448,7 @@ class DarlinEngine:
                          self.prog_peer.data_ptr(), self.world, self.eval_scratch.data_ptr(),
                          self.prof.data_ptr() if self.cfg.profile_phases else None)
         else:
+            self.use_split_protocol()
             self._enqueue_split(n_steps)
         if self.world > 1:
             from .._lib import check, cuda_lib, current_stream
@@ -596,6 +638,7 @@ def run_pass_lockstep(engines: list, order: list, kkt_threshold: float, reset: b
     """
     n_steps = 0
     for e in engines:
+        e.use_split_protocol()
         n_steps = e.stage_pass(order, kkt_threshold, reset, n_prior)
     for e in engines:
         K.pass_begin(e.wk, e.sv, e.ctrl_dev.data_ptr())
