@@ -552,6 +552,141 @@ __device__ __forceinline__ double update_coord(const psb_darlin_server& S, const
   return vio;
 }
 
+// ---- fused multi-rank pass: landing slots that are their own arrival flags --------------------
+// A worker's push is two plain 8-byte peer stores (g, u).  The server thread of a coordinate
+// polls the slots of the workers that hold the column (S.has) until neither is the EMPTY
+// pattern, stores EMPTY back, reduces in worker order (bit-reproducible), applies the proximal
+// update and stores (w, dw) into every such worker's mirror.  No ticket, no push flag, no
+// system fence on the push side: the NVLink flight of the pushes overlaps the local grid
+// barrier that separates the margin reads of phase 1 from the margin updates of phase 3.
+// A slot is written at most once per visit of its block, and two visits are separated by
+// grid barriers on both sides, so the stored-back EMPTY is in L2 long before the next push.
+constexpr unsigned long long kEmptySlot = PSB_DARLIN_EMPTY_SLOT;
+constexpr uint32_t kSpinLimit = 1u << 26;  // ~10 s of polling: trap instead of hanging the GPU
+
+__device__ __forceinline__ double poll_slot(double* slot) {
+  unsigned long long bits;
+  uint32_t spins = 0;
+  while ((bits = *reinterpret_cast<volatile unsigned long long*>(slot)) == kEmptySlot) {
+    if (++spins > kSpinLimit) __trap();
+  }
+  return __longlong_as_double((long long)bits);
+}
+
+// A mirror entry is 32 bytes: {w.lo, seq, w.hi, seq} {dw.lo, seq, dw.hi, seq}.  Every 8-byte half
+// carries the low word of the step's sequence number, so a reader that finds the four tags
+// equal to the step it is in holds a complete, fresh (w, dw): no version flag, no system
+// fence, no reset (the next visit of the key carries another tag).  Only 8-byte single-copy
+// atomicity of the peer stores is assumed.
+__device__ __forceinline__ void mirror_store(void* entry, double w, double dw, uint32_t tag) {
+  const unsigned long long a = (unsigned long long)__double_as_longlong(w);
+  const unsigned long long b = (unsigned long long)__double_as_longlong(dw);
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %2};" ::"l"(entry), "r"((uint32_t)a),
+               "r"(tag), "r"((uint32_t)(a >> 32)) : "memory");
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %2};" ::"l"((char*)entry + 16),
+               "r"((uint32_t)b), "r"(tag), "r"((uint32_t)(b >> 32)) : "memory");
+}
+__device__ __forceinline__ void mirror_poll(const void* entry, uint32_t tag, double& w, double& dw) {
+  uint32_t a0, a1, a2, a3, b0, b1, b2, b3, spins = 0;
+  for (;;) {
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3) : "l"(entry) : "memory");
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(b0), "=r"(b1), "=r"(b2), "=r"(b3) : "l"((const char*)entry + 16) : "memory");
+    if (a1 == tag && a3 == tag && b1 == tag && b3 == tag) break;
+    if (++spins > kSpinLimit) __trap();
+  }
+  w = __longlong_as_double((long long)((unsigned long long)a0 | ((unsigned long long)a2 << 32)));
+  dw = __longlong_as_double((long long)((unsigned long long)b0 | ((unsigned long long)b2 << 32)));
+}
+
+// One group of `gs` lanes (the power of two >= n_workers) per coordinate: lane r polls worker
+// r's slots, every lane forms the same fixed-order sums and the same update, lane r stores
+// the result into worker r's mirror, lane 0 keeps the shard.
+__device__ __forceinline__ double server_phase_direct(const psb_darlin_server& S, const ServerHyper& h,
+                                                      const StepPlan& plan, int bps, int64_t tid,
+                                                      int64_t nthreads, uint32_t tag) {
+  const int64_t total = plan.pref[bps];
+  int gs = 1;
+  while (gs < S.n_workers) gs <<= 1;
+  const int lane = threadIdx.x & 31;
+  const int r = lane & (gs - 1);
+  const uint32_t gmask = (gs == 32 ? 0xffffffffu : ((1u << gs) - 1u)) << (lane & ~(gs - 1));
+  const int64_t grp = tid / gs, ngrp = nthreads / gs;
+  double vio_max = 0;
+  for (int64_t v = grp; v < total; v += ngrp) {
+    const int q = locate(plan, bps, v);
+    const int64_t k = plan.first[q] + (v - plan.pref[q]);
+    const uint32_t aw = __ldcg(S.active + (k >> 5));
+    const double w = __ldcg(S.w + k);
+    const double dl = __ldcg(S.delta + k);
+    const uint32_t has = __ldg(S.has + k);
+    // a worker pushes exactly when its copy of the active bit is set, and the two copies
+    // change together (the mark published below clears the workers' bits in their phase 3)
+    if (!(aw >> (k & 31) & 1u)) continue;
+    const bool mine = r < S.n_workers && (has >> r & 1u);
+    double gv = 0, uv = 0;
+    if (mine) {
+      const int64_t at = (int64_t)r * S.land_cap + k;
+      gv = poll_slot(S.land_g + at);
+      uv = poll_slot(S.land_u + at);
+      *reinterpret_cast<unsigned long long*>(S.land_g + at) = kEmptySlot;
+      *reinterpret_cast<unsigned long long*>(S.land_u + at) = kEmptySlot;
+    }
+    double g = 0, u = 0;
+    for (int i = 0; i < S.n_workers; ++i) {  // worker order: bit-reproducible
+      g += __shfl_sync(gmask, gv, i, gs);
+      u += __shfl_sync(gmask, uv, i, gs);
+    }
+    double w_new = nan_mark(), dw = 0;
+    if (is_marked(w)) {  // filtered earlier and not revived: keep both bit copies clear
+      if (r == 0) bit_clear_atomic(S.active, k);
+    } else {
+      u = u / h.eta + 1e-10;
+      const double g_pos = g + h.lambda, g_neg = g - h.lambda;
+      double d = -w, vio = 0;
+      bool filtered = false;
+      if (w == 0) {
+        if (g_pos < 0) {
+          vio = -g_pos;
+        } else if (g_neg > 0) {
+          vio = g_neg;
+        } else if (g_pos > h.thr && g_neg < -h.thr) {
+          filtered = true;
+        }
+      }
+      if (filtered) {
+        if (r == 0) bit_clear_atomic(S.active, k);
+      } else {
+        vio_max = fmax(vio_max, vio);
+        if (g_pos <= u * w) {
+          d = -g_pos / u;
+        } else if (g_neg >= u * w) {
+          d = -g_neg / u;
+        }
+        d = fmin(dl, fmax(-dl, d));
+        if (r == 0) S.delta[k] = fmin(h.delta_max, 2 * fabs(d) + .1);
+        w_new = w + d;
+        dw = w_new - w;
+      }
+      if (r == 0) {
+        S.w[k] = w_new;
+        S.dw[k] = dw;
+      }
+    }
+    if (mine) mirror_store(S.mir[r] + 32 * k, w_new, dw, tag);  // peer store when r != rank
+  }
+  return vio_max;
+}
+
+__device__ __forceinline__ void spin_flag_ge(const uint64_t* flag, uint64_t want) {
+  uint32_t spins = 0;
+  while (ld_acquire_sys(flag) < want) {
+    __nanosleep(20);
+    if (++spins > kSpinLimit) __trap();
+  }
+}
+
 // Everything about one segment that does not change during a pass, held in registers.  The
 // persistent kernel stages the first segment of every warp for step s+1 while it waits on the
 // last barrier of step s, and keeps it from phase 1 to phase 3 of the step: what remains on the
@@ -799,14 +934,14 @@ __device__ __forceinline__ double grad_phase_packed(const psb_darlin_worker& W, 
 
 template <bool BINARY, bool MIRROR>
 __device__ __forceinline__ void pull_segment(const psb_darlin_worker& W, const SegRegs& R,
-                                             double delta_max, int lane) {
+                                             double delta_max, int lane, uint32_t tag) {
   const uint32_t aw = __ldcg(W.active + (R.j >> 5));
+  if (MIRROR && !(aw >> (R.j & 31) & 1u)) return;  // nothing was pushed, nothing comes back
   double w_new = 0, d = 0;
   if (lane == 0) {
-    if (MIRROR) {  // stored here by the owner before it raised the version flag
-      const int64_t at = (int64_t)R.owner * W.mir_cap + R.off;
-      w_new = ld_volatile_f64(W.mir_w + at);
-      d = ld_volatile_f64(W.mir_dw + at);
+    if (MIRROR) {  // stored here by the owner; the tag of this step makes it valid
+      if (aw >> (R.j & 31) & 1u)
+        mirror_poll(W.mir + 32 * ((int64_t)R.owner * W.mir_cap + R.off), tag, w_new, d);
     } else {
       w_new = ld_volatile_f64(W.srv_w[R.owner] + R.off);
       d = ld_volatile_f64(W.srv_dw[R.owner] + R.off);
@@ -856,21 +991,21 @@ __device__ __forceinline__ void pull_segment(const psb_darlin_worker& W, const S
 template <bool BINARY, bool MIRROR>
 __device__ __forceinline__ void pull_phase_packed(const psb_darlin_worker& W, const StepPlan& plan,
                                                   int bps, double delta_max, int64_t gw, int64_t nw,
-                                                  int lane, const SegRegs& pre) {
+                                                  int lane, const SegRegs& pre, uint32_t tag = 0) {
   const int64_t total = plan.pref[bps];
   if (gw < total) {
     if (pre.v == gw) {
-      pull_segment<BINARY, MIRROR>(W, pre, delta_max, lane);
+      pull_segment<BINARY, MIRROR>(W, pre, delta_max, lane, tag);
     } else {
       SegRegs R;
       stage_segment<BINARY>(R, W, plan, bps, gw, lane);
-      pull_segment<BINARY, MIRROR>(W, R, delta_max, lane);
+      pull_segment<BINARY, MIRROR>(W, R, delta_max, lane, tag);
     }
   }
   for (int64_t v = gw + nw; v < total; v += nw) {
     SegRegs R;
     stage_segment<BINARY>(R, W, plan, bps, v, lane);
-    pull_segment<BINARY, MIRROR>(W, R, delta_max, lane);
+    pull_segment<BINARY, MIRROR>(W, R, delta_max, lane, tag);
   }
 }
 
@@ -921,103 +1056,6 @@ __device__ __forceinline__ double server_phase_ilp(const psb_darlin_server& S, c
     S.dw[k] = w_new - w;
   }
   return vio_max;
-}
-
-// ---- fused multi-rank pass: landing slots that are their own arrival flags --------------------
-// A worker's push is two plain 8-byte peer stores (g, u).  The server thread of a coordinate
-// polls the slots of the workers that hold the column (S.has) until neither is the EMPTY
-// pattern, stores EMPTY back, reduces in worker order (bit-reproducible), applies the proximal
-// update and stores (w, dw) into every such worker's mirror.  No ticket, no push flag, no
-// system fence on the push side: the NVLink flight of the pushes overlaps the local grid
-// barrier that separates the margin reads of phase 1 from the margin updates of phase 3.
-// A slot is written at most once per visit of its block, and two visits are separated by
-// grid barriers on both sides, so the stored-back EMPTY is in L2 long before the next push.
-constexpr unsigned long long kEmptySlot = PSB_DARLIN_EMPTY_SLOT;
-constexpr uint32_t kSpinLimit = 1u << 26;  // ~10 s of polling: trap instead of hanging the GPU
-
-__device__ __forceinline__ double poll_slot(double* slot) {
-  unsigned long long bits;
-  uint32_t spins = 0;
-  while ((bits = *reinterpret_cast<volatile unsigned long long*>(slot)) == kEmptySlot) {
-    if (++spins > kSpinLimit) __trap();
-  }
-  return __longlong_as_double((long long)bits);
-}
-
-__device__ __forceinline__ double server_phase_direct(const psb_darlin_server& S, const ServerHyper& h,
-                                                      const StepPlan& plan, int bps, int64_t tid,
-                                                      int64_t nthreads) {
-  const int64_t total = plan.pref[bps];
-  double vio_max = 0;
-  for (int64_t v = tid; v < total; v += nthreads) {
-    const int q = locate(plan, bps, v);
-    const int64_t k = plan.first[q] + (v - plan.pref[q]);
-    const uint32_t aw = __ldcg(S.active + (k >> 5));
-    const double w = __ldcg(S.w + k);
-    const double dl = __ldcg(S.delta + k);
-    const uint32_t has = __ldg(S.has + k);
-    // a worker pushes exactly when its copy of the active bit is set, and the two copies
-    // change together (the mark published below clears the workers' bits in their phase 3)
-    if (!(aw >> (k & 31) & 1u)) continue;
-    double g = 0, u = 0;
-    for (int r = 0; r < S.n_workers; ++r) {
-      if (!(has >> r & 1u)) continue;
-      const int64_t at = (int64_t)r * S.land_cap + k;
-      g += poll_slot(S.land_g + at);
-      u += poll_slot(S.land_u + at);
-      *reinterpret_cast<unsigned long long*>(S.land_g + at) = kEmptySlot;
-      *reinterpret_cast<unsigned long long*>(S.land_u + at) = kEmptySlot;
-    }
-    if (is_marked(w)) {  // filtered earlier and not revived: keep both bit copies clear
-      bit_clear_atomic(S.active, k);
-      continue;
-    }
-    u = u / h.eta + 1e-10;
-    const double g_pos = g + h.lambda, g_neg = g - h.lambda;
-    double d = -w, vio = 0, w_new, dw;
-    bool filtered = false;
-    if (w == 0) {
-      if (g_pos < 0) {
-        vio = -g_pos;
-      } else if (g_neg > 0) {
-        vio = g_neg;
-      } else if (g_pos > h.thr && g_neg < -h.thr) {
-        filtered = true;
-      }
-    }
-    if (filtered) {
-      bit_clear_atomic(S.active, k);
-      w_new = nan_mark();
-      dw = 0;
-    } else {
-      vio_max = fmax(vio_max, vio);
-      if (g_pos <= u * w) {
-        d = -g_pos / u;
-      } else if (g_neg >= u * w) {
-        d = -g_neg / u;
-      }
-      d = fmin(dl, fmax(-dl, d));
-      S.delta[k] = fmin(h.delta_max, 2 * fabs(d) + .1);
-      w_new = w + d;
-      dw = w_new - w;
-    }
-    S.w[k] = w_new;
-    S.dw[k] = dw;
-    for (int r = 0; r < S.n_workers; ++r) {
-      if (!(has >> r & 1u)) continue;
-      S.mir_w[r][k] = w_new;  // peer store when r != rank
-      S.mir_dw[r][k] = dw;
-    }
-  }
-  return vio_max;
-}
-
-__device__ __forceinline__ void spin_flag_ge(const uint64_t* flag, uint64_t want) {
-  uint32_t spins = 0;
-  while (ld_acquire_sys(flag) < want) {
-    __nanosleep(20);
-    if (++spins > kSpinLimit) __trap();
-  }
 }
 
 __device__ __forceinline__ void prefetch_l2(const void* p) {
@@ -1156,42 +1194,27 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
     if (nkeys <= single_cta_keys) {
       // small step: one CTA (the one with the fewest segments) serves the shard
       if (blockIdx.x == G - 1 && nkeys > 0) {
-        double vio = server_phase_direct(S, h, P.sv, bps, threadIdx.x, kThreads);
+        double vio = server_phase_direct(S, h, P.sv, bps, threadIdx.x, kThreads, (uint32_t)seq);
         vio = warp_max(vio);
         if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
-        __syncthreads();
-        if (threadIdx.x < S.n_workers) {  // mirrors first, then the version (own rank included)
-          __threadfence_system();
-          st_release_sys(S.ver_flag[threadIdx.x], seq);
-        }
       }
       __syncthreads();
       if (has_next && do_prefetch) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
       PSB_PROF(1)
       grid_wait(bar, (uint32_t)(step + 1) * G);
     } else {
-      // large step: all CTAs share the coordinates, one more grid barrier before the flags
+      // large step: all CTAs share the coordinates
       __syncthreads();
-      PSB_PROF(1)
-      grid_wait(bar, (uint32_t)(step + 1) * G);
-      double vio = server_phase_direct(S, h, P.sv, bps, gt, nt);
+      if (has_next && do_prefetch) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
+      double vio = server_phase_direct(S, h, P.sv, bps, gt, nt, (uint32_t)seq);
       vio = warp_max(vio);
       if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
-      grid_arrive(bar + 3);
-      grid_wait(bar + 3, ++nbar * G);
-      if (blockIdx.x == G - 1 && threadIdx.x < S.n_workers) {
-        __threadfence_system();
-        st_release_sys(S.ver_flag[threadIdx.x], seq);
-      }
+      PSB_PROF(1)
+      grid_wait(bar, (uint32_t)(step + 1) * G);
     }
-    // ---- phase 3: wait for the owners' versions, then pull from the local mirror ----
-    if (P.wk.pref[bps] > 0) {
-      if (threadIdx.x < W.n_servers && (P.wk.mask >> threadIdx.x & 1u))
-        spin_flag_ge(W.ver_flag + threadIdx.x, seq);
-      __syncthreads();
-    }
+    // ---- phase 3: every warp polls the mirror entry of its column, then updates margins ----
     PSB_PROF(2)
-    pull_phase_packed<BINARY, true>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre);
+    pull_phase_packed<BINARY, true>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre, (uint32_t)seq);
     PSB_PROF(3)
     grid_arrive(bar + 2);
     pre.v = -1;
@@ -1379,7 +1402,7 @@ PSB_API int psb_darlin_fused_pass(const psb_darlin_worker* wk, const psb_darlin_
                   (void*)&scratch, (void*)&prof};
   const bool single = wk->n_workers == 1 && wk->n_servers == 1;
   if (!single)
-    PSB_REQUIRE(wk->mir_w && wk->mir_dw && wk->mir_cap > 0 && sv->has && sv->mir_w[0] && sv->mir_dw[0],
+    PSB_REQUIRE(wk->mir && wk->mir_cap > 0 && sv->has && sv->mir[0],
                 "psb_darlin_fused_pass: the multi-rank pass needs the mirrors and the holder masks "
                 "(worker.mir_*, server.mir_*, server.has) and EMPTY-filled landing slots");
   const void* fn = wk->sval

@@ -90,10 +90,9 @@ typedef struct psb_darlin_worker {
   const uint64_t* ver_flag;           /* local: [n_servers], written by the servers */
   const void* seg_meta;               /* [n_seg] int4 {col, len | first<<16 | single<<17, beg lo,
                                          beg hi}: one 16-byte load per segment (fused kernel) */
-  /* fused multi-rank pass: the servers store every updated coordinate into this worker's own
-   * mirror (index owner*mir_cap + col_off) before raising ver_flag, so the pull is local */
-  const double* mir_w;
-  const double* mir_dw;
+  /* fused multi-rank pass: the owners store every updated coordinate into this worker's own
+   * mirror (32-byte tagged entries, index owner*mir_cap + col_off), so the pull is local */
+  const char* mir;
   int64_t mir_cap;
 } psb_darlin_worker;
 
@@ -114,8 +113,7 @@ typedef struct psb_darlin_server {
   int32_t rank, n_workers, n_servers;
   uint64_t* ver_flag[PSB_MAX_PEERS];  /* on worker r: &ver_flag_r[rank] */
   /* fused multi-rank pass */
-  double* mir_w[PSB_MAX_PEERS];       /* on worker r: &mir_w_r[rank*mir_cap] */
-  double* mir_dw[PSB_MAX_PEERS];
+  char* mir[PSB_MAX_PEERS];           /* on worker r: &mir_r[32*rank*mir_cap] */
   const uint32_t* has;                /* [n_keys] bit r set: worker r holds nonzeros of the key */
 } psb_darlin_server;
 

@@ -297,7 +297,7 @@ class DarlinEngine:
         cap = max(max(self.shard_len), 1)
         self.land_cap = cap
         self.bps = max(1, min(cfg.max_block_delay + 1, 32))
-        nbytes = (2 * W * cap + 2 * cap + 2 * W * cap) * 8 + (2 * W + 4 * W) * 8 + W * 48 + 64 * 256
+        nbytes = (2 * W * cap + 2 * cap + 4 * W * cap) * 8 + (2 * W + 4 * W) * 8 + W * 48 + 64 * 256
         self.arena = self.comm.make_arena(nbytes, dev)
         A = self.arena
         self.b_land_g = A.alloc("land_g", W * cap, torch.float64)
@@ -305,8 +305,7 @@ class DarlinEngine:
         self.b_w = A.alloc("w", cap, torch.float64)
         self.b_dw = A.alloc("dw", cap, torch.float64)
         # fused multi-rank pass: mirrors of every shard, written by the owners (psb200.h)
-        self.b_mir_w = A.alloc("mir_w", W * cap, torch.float64)
-        self.b_mir_dw = A.alloc("mir_dw", W * cap, torch.float64)
+        self.b_mir = A.alloc("mirror", 4 * W * cap, torch.float64)  # 32-byte tagged entries
         self.b_push_flag = A.alloc("push_flag", W, torch.int64)
         self.b_ver_flag = A.alloc("ver_flag", W, torch.int64)
         self.b_bar_flag = A.alloc("bar_flag", W, torch.int64)
@@ -366,7 +365,7 @@ class DarlinEngine:
             wk.srv_dw[s] = A.peer_ptr(s, self.b_dw)
         wk.ver_flag = self.b_ver_flag.ptr
         wk.seg_meta = self.seg_meta.data_ptr()
-        wk.mir_w, wk.mir_dw, wk.mir_cap = self.b_mir_w.ptr, self.b_mir_dw.ptr, cap
+        wk.mir, wk.mir_cap = self.b_mir.ptr, cap
         self.wk = wk
 
         sv = K.DarlinServer()
@@ -378,8 +377,7 @@ class DarlinEngine:
         sv.n_keys, sv.rank, sv.n_workers, sv.n_servers = n_keys, self.rank, W, W
         for r in range(W):
             sv.ver_flag[r] = A.peer_ptr(r, self.b_ver_flag, self.rank)
-            sv.mir_w[r] = A.peer_ptr(r, self.b_mir_w, self.rank * cap)
-            sv.mir_dw[r] = A.peer_ptr(r, self.b_mir_dw, self.rank * cap)
+            sv.mir[r] = A.peer_ptr(r, self.b_mir, 4 * self.rank * cap)
         self.srv_has = self._holder_masks()
         sv.has = self.srv_has.data_ptr()
         self.direct_landing = bool(cfg.fused and W > 1 and self.grid_fused > 0)

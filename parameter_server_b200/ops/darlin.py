@@ -33,7 +33,7 @@ class DarlinWorker(C.Structure):
                 ("land_g", P * MAX_PEERS), ("land_u", P * MAX_PEERS),
                 ("land_cap", C.c_int64 * MAX_PEERS), ("push_flag", P * MAX_PEERS),
                 ("srv_w", P * MAX_PEERS), ("srv_dw", P * MAX_PEERS), ("ver_flag", P),
-                ("seg_meta", P), ("mir_w", P), ("mir_dw", P), ("mir_cap", C.c_int64)]
+                ("seg_meta", P), ("mir", P), ("mir_cap", C.c_int64)]
 
 
 class DarlinServer(C.Structure):
@@ -41,7 +41,7 @@ class DarlinServer(C.Structure):
                 ("land_cap", C.c_int64), ("push_flag", P), ("blk_rng", P), ("violation", P),
                 ("done_ctr", P), ("n_keys", C.c_int64), ("rank", C.c_int32),
                 ("n_workers", C.c_int32), ("n_servers", C.c_int32),
-                ("ver_flag", P * MAX_PEERS), ("mir_w", P * MAX_PEERS), ("mir_dw", P * MAX_PEERS),
+                ("ver_flag", P * MAX_PEERS), ("mir", P * MAX_PEERS),
                 ("has", P)]
 
 EMPTY_SLOT = 0x7ff8dead5107e001  # include/psb200.h PSB_DARLIN_EMPTY_SLOT

@@ -56,7 +56,9 @@ def main():
             ref.append((p.objective, p.nnz_w, p.nnz_active_set, p.violation))
             thr = p.violation / n_ex * 0.5
         for a, b in zip(objs, ref):
-            ok &= abs(a[0] - b[0]) <= 1e-9 * abs(b[0]) and a[1] == b[1] and a[2] == b[2]
+            # the persistent kernel evaluates exp / reciprocal with its own <=1.5 ulp routines, the
+            # split kernels with the library's: trajectories agree to rounding noise, not bitwise
+            ok &= abs(a[0] - b[0]) <= 1e-7 * abs(b[0]) and a[1] == b[1] and a[2] == b[2]
         detail = {"multi": objs, "emulated": ref}
     dist.barrier()
     if rank == 0:
