@@ -809,7 +809,7 @@ template <bool BINARY, bool SINGLE>
 __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const psb_darlin_server& S,
                                                const ServerHyper& h, const SegRegs& R, int lane,
                                                const double* __restrict__ exp_tab,
-                                               unsigned long long* tp = nullptr) {
+                                               unsigned long long* tp = nullptr, int dbg = 0) {
   unsigned long long t0 = 0, t1 = 0, t2 = 0, t3 = 0, t4 = 0;
   if (tp) t0 = stamp_after(0.0);
   // one latency level: active word, trust region, the margins and (single rank) the coordinate
@@ -830,6 +830,7 @@ __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const
 #pragma unroll
   for (int k = 0; k < kUnroll; ++k) { idx[k] = R.idx[k]; sv[k] = R.sv[k]; }
   for (int base = 0; base < R.len; base += 32 * kUnroll) {
+    if (dbg & 16) { g = 1e-3 * sv[0]; u = 1.0; break; }  // timing experiment only
     if (base > 0) {
 #pragma unroll
       for (int k = 0; k < kUnroll; ++k) {
@@ -847,6 +848,11 @@ __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const
 #pragma unroll
     for (int k = 0; k < kUnroll; ++k) zz[k] = idx[k] != 0xffffffffu ? __ldcg(W.z + idx[k]) : 0.0;
     if (tp && base == 0) t1 = stamp_after(zz[0] + zz[1] + zz[2] + zz[3] + d + sw + sdl);
+    if (dbg & 32) {  // timing experiment only: the gather without the arithmetic
+#pragma unroll
+      for (int k = 0; k < kUnroll; ++k) { g -= 1e-3 * zz[k] + 0.5 * (double)sv[k]; u += 1.0; }
+      continue;
+    }
     // branch-free over the batch so the four exp/divide chains interleave (fp64 latency bound);
     // a padding entry has x == 0 and contributes exactly nothing
     double tau[kUnroll], x[kUnroll], cv[kUnroll];
@@ -912,29 +918,29 @@ __device__ __forceinline__ double grad_phase_packed(const psb_darlin_worker& W, 
                                                     const ServerHyper& h, const StepPlan& plan,
                                                     int bps, int64_t gw, int64_t nw, int lane,
                                                     const SegRegs& pre, const double* __restrict__ exp_tab,
-                                                    unsigned long long* tp = nullptr) {
+                                                    unsigned long long* tp = nullptr, int dbg = 0) {
   const int64_t total = plan.pref[bps];
   double vio_max = 0;
   if (gw < total) {
     if (pre.v == gw) {
-      vio_max = grad_segment<BINARY, SINGLE>(W, S, h, pre, lane, exp_tab, tp);
+      vio_max = grad_segment<BINARY, SINGLE>(W, S, h, pre, lane, exp_tab, tp, dbg);
     } else {
       SegRegs R;
       stage_segment<BINARY>(R, W, plan, bps, gw, lane);
-      vio_max = grad_segment<BINARY, SINGLE>(W, S, h, R, lane, exp_tab);
+      vio_max = grad_segment<BINARY, SINGLE>(W, S, h, R, lane, exp_tab, nullptr, dbg);
     }
   }
   for (int64_t v = gw + nw; v < total; v += nw) {
     SegRegs R;
     stage_segment<BINARY>(R, W, plan, bps, v, lane);
-    vio_max = fmax(vio_max, grad_segment<BINARY, SINGLE>(W, S, h, R, lane, exp_tab));
+    vio_max = fmax(vio_max, grad_segment<BINARY, SINGLE>(W, S, h, R, lane, exp_tab, nullptr, dbg));
   }
   return vio_max;
 }
 
 template <bool BINARY, bool MIRROR>
 __device__ __forceinline__ void pull_segment(const psb_darlin_worker& W, const SegRegs& R,
-                                             double delta_max, int lane, uint32_t tag) {
+                                             double delta_max, int lane, uint32_t tag, int tag_dbg = 0) {
   const uint32_t aw = __ldcg(W.active + (R.j >> 5));
   if (MIRROR && !(aw >> (R.j & 31) & 1u)) return;  // nothing was pushed, nothing comes back
   double w_new = 0, d = 0;
@@ -961,7 +967,7 @@ __device__ __forceinline__ void pull_segment(const psb_darlin_worker& W, const S
     W.w[R.j] = w_new;
     W.delta[R.j] = fmin(delta_max, 2 * fabs(d) + .1);
   }
-  if (d == 0) return;
+  if (d == 0 || (tag_dbg & 8)) return;
   uint32_t idx[kUnroll];
   float sv[kUnroll];
 #pragma unroll
@@ -991,21 +997,21 @@ __device__ __forceinline__ void pull_segment(const psb_darlin_worker& W, const S
 template <bool BINARY, bool MIRROR>
 __device__ __forceinline__ void pull_phase_packed(const psb_darlin_worker& W, const StepPlan& plan,
                                                   int bps, double delta_max, int64_t gw, int64_t nw,
-                                                  int lane, const SegRegs& pre, uint32_t tag = 0) {
+                                                  int lane, const SegRegs& pre, uint32_t tag = 0, int dbg = 0) {
   const int64_t total = plan.pref[bps];
   if (gw < total) {
     if (pre.v == gw) {
-      pull_segment<BINARY, MIRROR>(W, pre, delta_max, lane, tag);
+      pull_segment<BINARY, MIRROR>(W, pre, delta_max, lane, tag, dbg);
     } else {
       SegRegs R;
       stage_segment<BINARY>(R, W, plan, bps, gw, lane);
-      pull_segment<BINARY, MIRROR>(W, R, delta_max, lane, tag);
+      pull_segment<BINARY, MIRROR>(W, R, delta_max, lane, tag, dbg);
     }
   }
   for (int64_t v = gw + nw; v < total; v += nw) {
     SegRegs R;
     stage_segment<BINARY>(R, W, plan, bps, v, lane);
-    pull_segment<BINARY, MIRROR>(W, R, delta_max, lane, tag);
+    pull_segment<BINARY, MIRROR>(W, R, delta_max, lane, tag, dbg);
   }
 }
 
@@ -1078,6 +1084,19 @@ __device__ __forceinline__ void prefetch_step(const psb_darlin_worker& W, const 
 }
 
 
+// The thread that signals and polls the grid barriers of a step: lane 0 of the last warp, which
+// owns a segment only in steps with more than (kWarps-1) * grid segments.  The other warps use
+// the barrier's flight time for the next steps' plan, L2 prefetch and register staging.
+constexpr int kSpinner = (kWarps - 1) * 32;
+__device__ __forceinline__ void grid_arrive_by(uint32_t* ctr, int leader) {
+  __syncthreads();
+  if (threadIdx.x == leader) red_release_gpu_add(ctr, 1u);
+}
+__device__ __forceinline__ void grid_wait_by(const uint32_t* ctr, uint32_t target, int leader) {
+  if (threadIdx.x == leader) spin_gpu_ge(ctr, target);
+  __syncthreads();
+}
+
 // bar[0] phase-1 arrivals, bar[1] "server done" step stamp, bar[2] phase-3 arrivals,
 // bar[3] generic barrier (begin / large steps / evaluate).  All zero between launches.
 constexpr int64_t kSingleCtaServerKeys = 16 * kThreads;
@@ -1089,7 +1108,7 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
               const int64_t* __restrict__ blk_tab, int n_steps, int bps, uint32_t* bar,
               psb_darlin_progress* out_local, psb_darlin_progress* const* out_peer, int n_peers,
               double* scratch, unsigned long long* prof) {
-  __shared__ FusedPlan plans[2];
+  __shared__ FusedPlan plans[3];  // steps s, s+1, s+2: built two steps ahead, off the critical path
   __shared__ double sh[4][kWarps];
   __shared__ double exp_tab[kExpTab];
   fill_exp_table(exp_tab);
@@ -1116,6 +1135,7 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
   const ServerHyper h{ctrl->lambda, ctrl->eta, ctrl->delta_max, ctrl->kkt_threshold};
   const uint64_t seq_base = ctrl->seq_base;
   const bool do_prefetch = !(ctrl->flags & 1);
+  const int dbg = ctrl->flags;  // bits 8 / 16: timing experiments (wrong results), see bench.py
   const int64_t single_cta_keys = ctrl->server_cta_keys > 0 ? ctrl->server_cta_keys : kSingleCtaServerKeys;
 
   // ---- pass begin (ref darlin.h:176-182, 297-300) ----
@@ -1134,20 +1154,21 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
         if (is_marked(__ldcg(S.w + i))) S.w[i] = 0;
   }
   if (wid == 0 && n_steps > 0) fused_plan(plans[0], blk_tab, order, 0, bps);
+  if (wid == 1 && n_steps > 1) fused_plan(plans[1], blk_tab, order, 1, bps);
   grid_arrive(bar + 3);
   if (n_steps > 0 && gw < plans[0].wk.pref[bps]) stage_segment<BINARY>(pre, W, plans[0].wk, bps, gw, lane);
   grid_wait(bar + 3, ++nbar * G);
 
   for (int step = 0; step < n_steps; ++step) {
-    const FusedPlan& P = plans[step & 1];
-    const FusedPlan& Pn = plans[(step + 1) & 1];
+    const FusedPlan& P = plans[step % 3];
+    const FusedPlan& Pn = plans[(step + 1) % 3];
     const uint64_t seq = seq_base + (uint64_t)step + 1;
     const int64_t nkeys = P.sv.pref[bps];
     const bool has_next = step + 1 < n_steps;
     // ---- phase 1: gradient + push ----
     {
       unsigned long long* tp = (prof && wid == 0) ? prof + 8 + 2 * (unsigned long long)n_steps + 2 * 4096 + 8 * (blockIdx.x & 7) : nullptr;
-      const double vio = grad_phase_packed<BINARY, SINGLE>(W, S, h, P.wk, bps, gw, nw, lane, pre, exp_tab, tp);
+      const double vio = grad_phase_packed<BINARY, SINGLE>(W, S, h, P.wk, bps, gw, nw, lane, pre, exp_tab, tp, dbg);
       if (SINGLE && vio > 0) atomic_max_nonneg(S.violation, vio);
     }
     if (prof && threadIdx.x == 0) {  // per-step straggler: max phase-1 time and its CTA
@@ -1165,32 +1186,31 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
     if (SINGLE) {
       // one rank: the shard was updated column by column inside phase 1; a single grid
       // barrier separates the margin reads of phase 1 from the margin updates of phase 3
-      grid_arrive(bar);
-      if (wid == 0 && has_next) fused_plan(plans[(step + 1) & 1], blk_tab, order, step + 1, bps);
-      __syncthreads();
-      if (has_next && do_prefetch) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
+      grid_arrive_by(bar, kSpinner);
+      if (wid == 1 && step + 2 < n_steps) fused_plan(plans[(step + 2) % 3], blk_tab, order, step + 2, bps);
+      if (has_next && do_prefetch && wid != kWarps - 1) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
       PSB_PROF(1)
-      grid_wait(bar, (uint32_t)(step + 1) * G);
+      grid_wait_by(bar, (uint32_t)(step + 1) * G, kSpinner);
       PSB_PROF(2)
-      pull_phase_packed<BINARY, false>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre);
+      pull_phase_packed<BINARY, false>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre, 0, dbg);
       if (prof && threadIdx.x == 0) {
         unsigned long long now_;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
         atomicMax(prof + 9 + 2 * step, ((now_ - t_mark) << 20) | blockIdx.x);
       }
       PSB_PROF(3)
-      grid_arrive(bar + 2);
+      grid_arrive_by(bar + 2, kSpinner);
       pre.v = -1;
-      if (has_next && gw < Pn.wk.pref[bps]) stage_segment<BINARY>(pre, W, Pn.wk, bps, gw, lane);
-      grid_wait(bar + 2, (uint32_t)(step + 1) * G);
+      if (has_next && wid != kWarps - 1 && gw < Pn.wk.pref[bps]) stage_segment<BINARY>(pre, W, Pn.wk, bps, gw, lane);
+      grid_wait_by(bar + 2, (uint32_t)(step + 1) * G, kSpinner);
       PSB_PROF(4)
       continue;
     }
     // ---- more than one rank ----
     // barrier A (local): every margin read of phase 1 precedes every margin update of phase 3.
     // The pushes are already in flight; the shard update runs between arrive and wait.
-    grid_arrive(bar);
-    if (wid == 0 && has_next) fused_plan(plans[(step + 1) & 1], blk_tab, order, step + 1, bps);
+    grid_arrive_by(bar, kSpinner);
+    if (wid == 1 && step + 2 < n_steps) fused_plan(plans[(step + 2) % 3], blk_tab, order, step + 2, bps);
     if (nkeys <= single_cta_keys) {
       // small step: one CTA (the one with the fewest segments) serves the shard
       if (blockIdx.x == G - 1 && nkeys > 0) {
@@ -1198,28 +1218,26 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
         vio = warp_max(vio);
         if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
       }
-      __syncthreads();
-      if (has_next && do_prefetch) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
+      if (has_next && do_prefetch && wid != kWarps - 1) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
       PSB_PROF(1)
-      grid_wait(bar, (uint32_t)(step + 1) * G);
+      grid_wait_by(bar, (uint32_t)(step + 1) * G, kSpinner);
     } else {
       // large step: all CTAs share the coordinates
-      __syncthreads();
       if (has_next && do_prefetch) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
       double vio = server_phase_direct(S, h, P.sv, bps, gt, nt, (uint32_t)seq);
       vio = warp_max(vio);
       if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
       PSB_PROF(1)
-      grid_wait(bar, (uint32_t)(step + 1) * G);
+      grid_wait_by(bar, (uint32_t)(step + 1) * G, kSpinner);
     }
     // ---- phase 3: every warp polls the mirror entry of its column, then updates margins ----
     PSB_PROF(2)
-    pull_phase_packed<BINARY, true>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre, (uint32_t)seq);
+    pull_phase_packed<BINARY, true>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre, (uint32_t)seq, dbg);
     PSB_PROF(3)
-    grid_arrive(bar + 2);
+    grid_arrive_by(bar + 2, kSpinner);
     pre.v = -1;
-    if (has_next && gw < Pn.wk.pref[bps]) stage_segment<BINARY>(pre, W, Pn.wk, bps, gw, lane);
-    grid_wait(bar + 2, (uint32_t)(step + 1) * G);
+    if (has_next && wid != kWarps - 1 && gw < Pn.wk.pref[bps]) stage_segment<BINARY>(pre, W, Pn.wk, bps, gw, lane);
+    grid_wait_by(bar + 2, (uint32_t)(step + 1) * G, kSpinner);
     PSB_PROF(4)
   }
   if (prof && threadIdx.x == 0)
