@@ -1,4 +1,5 @@
 #include "system/runtime.h"
+#include "util/local_machine.h"
 
 #include <list>
 
@@ -645,12 +646,47 @@ static bool parseNode(const string& text, Node* node) {
   return true;
 }
 
+// MPI-style launch: every process gets the same command line plus -my_rank.  Rank 0 is the
+// scheduler, ranks 1..W the workers, then the servers, then the hot spares; each one finds
+// its own address and a free port (ref van.cc:235-278, script/mpi_node.sh).
+static Node assembleMyNode(const Node& scheduler) {
+  if (FLAGS_my_rank == 0) return scheduler;
+  Node node;
+  const int r = FLAGS_my_rank;
+  if (r <= FLAGS_num_workers) {
+    node.set_role(NodeView::WORKER);
+    node.set_id("W" + std::to_string(r - 1));
+  } else if (r <= FLAGS_num_workers + FLAGS_num_servers) {
+    node.set_role(NodeView::SERVER);
+    node.set_id("S" + std::to_string(r - FLAGS_num_workers - 1));
+  } else {
+    node.set_role(NodeView::UNUSED);
+    node.set_id("U" + std::to_string(r - FLAGS_num_workers - FLAGS_num_servers - 1));
+  }
+  string interface = FLAGS_interface, ip;
+  if (interface.empty()) {
+    CHECK(LocalMachine::pickupAvailableInterfaceAndIP(&interface, &ip)) << "no usable network interface";
+  } else {
+    ip = LocalMachine::IP(interface);
+    CHECK(!ip.empty()) << "interface [" << interface << "] has no IPv4 address";
+  }
+  const unsigned short port = LocalMachine::pickupAvailablePort();
+  CHECK_NE(port, 0) << "no free port on " << ip;
+  node.set_hostname(ip);
+  node.set_port(port);
+  return node;
+}
+
 void Postoffice::start(int* argc, char*** argv) {
   string err;
   CHECK(FlagRegistry::get().parse(argc, argv, true, &err)) << err;
   PostofficeOptions o;
-  CHECK(parseNode(FLAGS_my_node, &o.my_node));
   CHECK(parseNode(FLAGS_scheduler, &o.scheduler));
+  if (FLAGS_my_rank >= 0) {
+    o.my_node = assembleMyNode(o.scheduler);
+  } else {
+    CHECK(parseNode(FLAGS_my_node, &o.my_node));
+  }
   if (FLAGS_bind_to) o.my_node.set_port(FLAGS_bind_to);
   o.num_servers = FLAGS_num_servers;
   o.num_workers = FLAGS_num_workers;
