@@ -443,6 +443,182 @@ PSH_API int psh_run_kv_cluster(int32_t num_servers, int32_t num_workers, int32_t
   return 0;
 }
 
+// ---- fault-tolerance scenarios (in-process clusters) ---------------------------------------------------
+namespace {
+struct Gate {
+  std::mutex mu;
+  std::condition_variable cv;
+  int stage = 0;
+  void set(int s) { { Lock l(mu); stage = s; } cv.notify_all(); }
+  void wait(int s) { std::unique_lock<std::mutex> l(mu); cv.wait(l, [&] { return stage >= s; }); }
+};
+// a server whose shard can be reloaded from the replica holders
+static Key spreadKey(int i, int n) { return (Key)i * (~(Key)0 / (Key)n); }  // covers every shard
+class ReplServerApp : public KVServerApp {
+ public:
+  using KVServerApp::KVServerApp;
+  void init() override {
+    Range<Key> mine = myKeyRange();
+    SArray<Key> key;
+    SArray<float> val;
+    for (int i = 0; i < n_; ++i)
+      if (mine.contains(spreadKey(i, n_))) { key.pushBack(spreadKey(i, n_)); val.pushBack(0.1f * i); }
+    vec_.key() = key;
+    vec_.value() = val;
+  }
+  void recover() override { vec_.recover(myKeyRange()); }
+};
+class ReplWorkerApp : public App {
+ public:
+  ReplWorkerApp(const string& name, int n, std::vector<float>* out, Gate* gate)
+      : App(name), vec_("w", name), n_(n), out_(out), gate_(gate) {}
+  ~ReplWorkerApp() { stopExecutor(); }
+  void run() override {
+    SArray<Key> key;
+    for (int k = 0; k < n_; ++k) key.pushBack(spreadKey(k, n_));
+    vec_.key() = key;
+    MessagePtr push(new Message(kServerGroup));
+    push->setKey(key);
+    push->addValue(SArray<float>(key.size(), 1.0f));
+    vec_.waitOutMsg(kServerGroup, vec_.push(push));
+    gate_->set(1);   // pushed and acknowledged: the driver may now kill a server
+    gate_->wait(2);  // a spare took the dead server's place
+    MessagePtr pull(new Message(kServerGroup));
+    pull->setKey(key);
+    vec_.waitOutMsg(kServerGroup, vec_.pull(pull));
+    SArray<float> v = vec_.value();
+    out_->assign(v.begin(), v.end());
+  }
+  KVVector<Key, float> vec_;
+  int n_;
+  std::vector<float>* out_;
+  Gate* gate_;
+};
+class SleepWorkerApp : public App {
+ public:
+  SleepWorkerApp(const string& name, int ms) : App(name), ms_(ms) {}
+  void run() override { std::this_thread::sleep_for(std::chrono::milliseconds(ms_)); }
+  int ms_;
+};
+
+struct MiniCluster {
+  std::vector<Node> nodes;
+  std::vector<unique_ptr<Postoffice>> offices;
+  std::vector<std::thread> threads;
+  shared_ptr<InprocFabric> fabric = std::make_shared<InprocFabric>();
+  void add(NodeView::Role r, const string& id) {
+    Node n;
+    n.set_role(r);
+    n.set_id(id);
+    n.set_hostname("127.0.0.1");
+    n.set_port(1000 + (int)nodes.size());
+    nodes.push_back(n);
+  }
+  int index(const string& id) const {
+    for (size_t i = 0; i < nodes.size(); ++i) if (nodes[i].id() == id) return (int)i;
+    return -1;
+  }
+  void launch(int num_servers, int num_workers, int num_unused, int report_interval, App::Factory factory) {
+    offices.resize(nodes.size());
+    for (auto& o : offices) o.reset(new Postoffice());
+    for (size_t i = 0; i < nodes.size(); ++i) {
+      threads.emplace_back([=] {
+        PostofficeOptions opt;
+        opt.my_node = nodes[i];
+        opt.scheduler = nodes[0];
+        opt.num_servers = num_servers;
+        opt.num_workers = num_workers;
+        opt.num_unused = num_unused;
+        opt.report_interval = report_interval;
+        opt.fabric = fabric;
+        opt.factory = factory;
+        opt.print_van = getenv("PSH_PRINT_VAN") != nullptr;
+        offices[i]->start(opt);
+        offices[i]->stop();
+      });
+    }
+  }
+  void join() {
+    for (auto& t : threads) t.join();
+    offices.clear();
+  }
+};
+}  // namespace
+
+// Servers S0,S1 hold keys 0..n-1 (value 0.1*key) with one replica each, a spare U0 idles.  The
+// worker adds 1 to every key; then S1 is killed, the scheduler swaps U0 in (ManageNode::REPLACE),
+// U0 reloads S1's shard from the replica holder, and the worker pulls all keys.
+// out_vals[k]: 0.1*k + 1 on the surviving shard, 1 (= what the replica saw pushed) on the recovered one.
+PSH_API int psh_run_replace_scenario(int32_t n_keys, float* out_vals, uint64_t* s1_range2) {
+  const int saved = FLAGS_num_replicas;
+  FLAGS_num_replicas = 1;
+  std::vector<float> got;
+  Gate gate;
+  MiniCluster c;
+  c.add(NodeView::SCHEDULER, "H");
+  c.add(NodeView::SERVER, "S0");
+  c.add(NodeView::SERVER, "S1");
+  c.add(NodeView::WORKER, "W0");
+  c.add(NodeView::UNUSED, "U0");
+  auto factory = [&](const string& name, const string&) -> App* {
+    NodeView me = Postoffice::current().myNode();
+    if (me.role() == NodeView::SERVER) return new ReplServerApp(name, n_keys);
+    if (me.role() == NodeView::WORKER) return new ReplWorkerApp(name, n_keys, &got, &gate);
+    return new App(name);
+  };
+  c.launch(2, 1, 1, 0, factory);
+  gate.wait(1);
+  Postoffice& sched = *c.offices[0];
+  Node dead, live;
+  for (int tries = 0; tries < 500 && live.id().empty(); ++tries) {  // the spare may connect late
+    for (const auto& n : sched.yp().nodes()) {
+      if (n.id() == "S1") dead = n;
+      if (n.id() == "U0") live = n;
+    }
+    if (live.id().empty()) std::this_thread::sleep_for(std::chrono::milliseconds(10));
+  }
+  if (live.id().empty() || dead.id().empty()) return fail("spare or victim never registered");
+  // which of the n spread keys live on S1
+  if (s1_range2) {
+    Range<Key> r(dead.key().begin(), dead.key().end());
+    int lo = n_keys, hi = 0;
+    for (int i = 0; i < n_keys; ++i)
+      if (r.contains(spreadKey(i, n_keys))) { lo = std::min(lo, i); hi = std::max(hi, i + 1); }
+    s1_range2[0] = lo; s1_range2[1] = hi;
+  }
+  c.offices[c.index("S1")]->kill();
+  sched.replaceNode(dead, live);
+  gate.set(2);
+  c.join();
+  FLAGS_num_replicas = saved;
+  if ((int)got.size() != n_keys) return fail("worker pulled " + to_string(got.size()) + " values");
+  for (int i = 0; i < n_keys; ++i) out_vals[i] = got[i];
+  return 0;
+}
+
+// Every node reports to the scheduler each `interval_s` seconds; returns the dashboard table
+// after `run_ms` and, in *n_dead, how many nodes look dead with a zero-second timeout margin
+// `dead_timeout_s` (a node that never reported is not counted).
+PSH_API int psh_run_heartbeat_scenario(int32_t interval_s, int32_t run_ms, int32_t dead_timeout_s,
+                                       char* out, int64_t cap, int64_t* len, int32_t* n_dead) {
+  MiniCluster c;
+  c.add(NodeView::SCHEDULER, "H");
+  c.add(NodeView::SERVER, "S0");
+  c.add(NodeView::WORKER, "W0");
+  c.add(NodeView::WORKER, "W1");
+  auto factory = [&](const string& name, const string&) -> App* {
+    NodeView me = Postoffice::current().myNode();
+    if (me.role() == NodeView::WORKER) return new SleepWorkerApp(name, run_ms);
+    return new App(name);
+  };
+  c.launch(1, 2, 0, interval_s, factory);
+  std::this_thread::sleep_for(std::chrono::milliseconds(run_ms * 9 / 10));
+  string rep = c.offices[0]->dashboardReport();
+  if (n_dead) *n_dead = (int32_t)c.offices[0]->deadNodes(dead_timeout_s).size();
+  c.join();
+  return put(rep, out, cap, len);
+}
+
 // ---- diagnostics ---------------------------------------------------------------------------------------
 #include <execinfo.h>
 #include <signal.h>

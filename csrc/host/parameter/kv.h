@@ -291,7 +291,8 @@ class KVVector : public SharedParameter<K> {
   // per-owner copies on replica holders
   void setReplica(const MessagePtr& msg) override {
     Lock l(rep_mu_);
-    auto& rep = replica_[msg->sender][msg->task.key_channel()];
+    // keyed by the owner's key range, not its node id: a replacement node asks for the range
+    auto& rep = replica_[Range<K>(msg->task.key_range().template to<K>()).begin()][msg->task.key_channel()];
     SArray<K> k(msg->key);
     if (msg->value.empty()) return;
     SArray<V> v(msg->value[0]);
@@ -299,8 +300,8 @@ class KVVector : public SharedParameter<K> {
   }
   void getReplica(const MessagePtr& msg) override {
     Lock l(rep_mu_);
-    // msg->recver is the node asking for its own (lost) shard
-    auto it = replica_.find(msg->recver);
+    // the request names the (lost) range
+    auto it = replica_.find(Range<K>(msg->task.key_range().template to<K>()).begin());
     SArray<K> k;
     SArray<V> v;
     if (it != replica_.end())
@@ -321,7 +322,7 @@ class KVVector : public SharedParameter<K> {
   std::mutex mu_, rep_mu_;
   std::unordered_map<int, SArray<K>> key_;
   std::unordered_map<int, SArray<V>> val_;
-  std::map<NodeID, std::map<int, std::map<K, V>>> replica_;
+  std::map<K, std::map<int, std::map<K, V>>> replica_;
   int val_entry_size_;
 };
 

@@ -528,6 +528,11 @@ Customer* YellowPages::customer(const string& name) {
   auto it = customers_.find(name);
   return it == customers_.end() ? nullptr : it->second;
 }
+Customer* YellowPages::customerIfPresent(const string& name) {
+  Lock l(mu_);
+  auto it = customers_.find(name);
+  return it == customers_.end() ? nullptr : it->second;
+}
 void YellowPages::depends(const string& child, const string& parent) {
   Lock l(mu_);
   relations_[parent].push_back(child);
@@ -747,6 +752,12 @@ void Postoffice::start(const PostofficeOptions& opt) {
     if (done_) return;
     CHECK(app_) << "INIT before ADD";
     app_->init();
+    bool recover = false;
+    {
+      Lock l(mu_);
+      recover = init_msg_ && init_msg_->task.msg() == "recover";
+    }
+    if (recover) app_->recover();
     finishBarrier(0);
     run_app_promise_.get_future().wait();
     if (done_) return;
@@ -946,7 +957,7 @@ void Postoffice::recv() {
         if (tk.mng_node().cmd() == ManageNodeView::CONNECT) continue;
       }
       // mark finished in the app's executor and acknowledge
-      Customer* c = yp_.customer(tk.customer());
+      Customer* c = yp_.customerIfPresent(tk.customer());
       if (c) {
         RNodePtr r = c->exec().rnode(msg->sender);
         if (r) r->finishIncomingTask(tk.time());
@@ -1027,11 +1038,12 @@ void Postoffice::manageNode(const TaskView& tk) {
     }
     case ManageNodeView::REPLACE: {  // node(0) died, node(1) takes over its role / rank / range
       CHECK_EQ(mng.node_size(), 2);
-      Customer* obj = yp_.customer(tk.customer());
-      if (!obj) break;
       yp_.removeNode(mng.node(0).id());
       yp_.addNode(mng.node(1));
+      // a spare learns its new role here, before its app exists (the factory looks at the role)
       if (mng.node(1).id() == opt_.my_node.id()) opt_.my_node = mng.node(1);
+      Customer* obj = yp_.customerIfPresent(tk.customer());
+      if (!obj) break;
       obj->exec().replace(mng.node(0), mng.node(1));
       for (const auto& c : yp_.childern(obj->name())) {
         Customer* child = yp_.customer(c);
@@ -1068,13 +1080,45 @@ void Postoffice::replaceNode(const NodeView& dead, const NodeView& live) {
   t.mutable_mng_node().add_node().raw()->copyFrom(*dead.raw());
   t.mutable_mng_node().add_node().raw()->copyFrom(*nw.raw());
   manageNode(t);
-  // the spare first needs the app, then everybody learns about the swap
+  // the spare needs its new identity, the app, then the node table (ranks, key ranges, replica
+  // wiring) ...
+  app_->port(nw.id())->submitAndWait(t);
   Task addapp;
   addapp.set_type(TaskView::MANAGE);
   addapp.mutable_mng_app().set_cmd(ManageAppView::ADD);
   addapp.mutable_mng_app().set_conf(opt_.app_conf);
   app_->port(nw.id())->submitAndWait(addapp);
+  Task table;
+  table.set_type(TaskView::MANAGE);
+  table.mutable_mng_node().set_cmd(ManageNodeView::ADD);
+  for (const auto& n : yp_.nodes())
+    if (n.role() != NodeView::UNUSED) table.mutable_mng_node().add_node().raw()->copyFrom(*n.raw());
+  app_->port(nw.id())->submitAndWait(table);
+  // ... everybody else swaps the dead node for it (unanswered requests are re-sent to it) ...
   app_->port(kLiveGroup)->submit(t);
+  // ... and it initialises, reloads the shard from the replica holders and runs
+  Task init;
+  init.set_type(TaskView::MANAGE);
+  init.set_msg("recover");
+  init.mutable_mng_app().set_cmd(ManageAppView::INIT);
+  app_->port(nw.id())->submitAndWait(init);
+  Task run;
+  run.set_type(TaskView::MANAGE);
+  run.mutable_mng_app().set_cmd(ManageAppView::RUN);
+  app_->port(nw.id())->submit(run);
+}
+
+string Postoffice::dashboardReport() { return dashboard_->report(); }
+
+void Postoffice::kill() {
+  {
+    Lock l(mu_);
+    done_ = true;
+  }
+  cv_.notify_all();
+  try { init_app_promise_.set_value(); } catch (...) {}
+  try { run_app_promise_.set_value(); } catch (...) {}
+  if (started_) yp_.van_->shutdown();
 }
 
 void Postoffice::removeNode(const NodeView& dead) {

@@ -215,6 +215,8 @@ class App : public Customer {
   virtual ~App() {}
   virtual void init() {}
   virtual void run() {}
+  // called after init() on a node that replaces a dead one: reload what the replicas hold
+  virtual void recover() {}
   // default: forwards to the process-wide factory (see setFactory)
   static App* create(const string& name, const string& conf);
   typedef std::function<App*(const string& name, const string& conf)> Factory;
@@ -226,7 +228,8 @@ class YellowPages {
  public:
   void add(Customer* obj);
   void remove(const string& name);
-  Customer* customer(const string& name);
+  Customer* customer(const string& name);           // waits a little for one under construction
+  Customer* customerIfPresent(const string& name);  // never waits
   void depends(const string& child, const string& parent);
   std::vector<string> childern(const string& parent);
   void addNode(const NodeView& node);
@@ -312,6 +315,10 @@ class Postoffice {
   void replaceNode(const NodeView& dead, const NodeView& live);
   void removeNode(const NodeView& dead);
   std::vector<string> deadNodes(int timeout_sec);
+  // the scheduler's table of the latest heartbeat reports (ref dashboard.cc)
+  string dashboardReport();
+  // what a crash looks like to this process: stop waiting, shut the van (fault-injection in tests)
+  void kill();
 
  private:
   void send();

@@ -215,3 +215,22 @@ def run_kv_cluster(num_servers: int, num_workers: int, n_keys: int, pull_keys, t
     hcheck(_lib().psh_run_kv_cluster(num_servers, num_workers, n_keys, _ptr(keys, C.c_uint64), keys.size,
                                      int(tcp), base_port, _ptr(out, C.c_float)))
     return out
+
+
+def run_replace_scenario(n_keys: int):
+    """Kill server S1 of a 2-server in-process cluster with replication and swap the spare U0 in
+    (ManageNode::REPLACE). Returns (values the worker pulls afterwards, S1's key range)."""
+    out = np.zeros(n_keys, dtype=np.float32)
+    rng = (C.c_uint64 * 2)()
+    hcheck(_lib().psh_run_replace_scenario(n_keys, _ptr(out, C.c_float), rng))
+    return out, (int(rng[0]), int(rng[1]))
+
+
+def run_heartbeat_scenario(interval_s: int = 1, run_ms: int = 2600, dead_timeout_s: int = 60):
+    """Returns (dashboard table of the scheduler, number of nodes overdue by dead_timeout_s)."""
+    buf = C.create_string_buffer(1 << 16)
+    n = C.c_int64(0)
+    dead = C.c_int32(0)
+    hcheck(_lib().psh_run_heartbeat_scenario(interval_s, run_ms, dead_timeout_s, buf, 1 << 16, C.byref(n),
+                                             C.byref(dead)))
+    return buf.raw[:n.value].decode(), int(dead.value)
