@@ -505,6 +505,7 @@ struct MiniCluster {
   std::vector<Node> nodes;
   std::vector<unique_ptr<Postoffice>> offices;
   std::vector<std::thread> threads;
+  std::vector<std::unique_ptr<std::atomic<int>>> state;  // 0 starting, 1 started, 2 stopped
   shared_ptr<InprocFabric> fabric = std::make_shared<InprocFabric>();
   void add(NodeView::Role r, const string& id) {
     Node n;
@@ -521,6 +522,7 @@ struct MiniCluster {
   void launch(int num_servers, int num_workers, int num_unused, int report_interval, App::Factory factory) {
     offices.resize(nodes.size());
     for (auto& o : offices) o.reset(new Postoffice());
+    for (size_t i = 0; i < nodes.size(); ++i) state.emplace_back(new std::atomic<int>(0));
     for (size_t i = 0; i < nodes.size(); ++i) {
       threads.emplace_back([=] {
         PostofficeOptions opt;
@@ -534,13 +536,32 @@ struct MiniCluster {
         opt.factory = factory;
         opt.print_van = getenv("PSH_PRINT_VAN") != nullptr;
         offices[i]->start(opt);
+        state[i]->store(1);
         offices[i]->stop();
+        state[i]->store(2);
       });
     }
   }
-  void join() {
-    for (auto& t : threads) t.join();
-    offices.clear();
+  // empty string: every node stopped; otherwise the nodes that did not within `seconds` (their
+  // threads and postoffices are leaked on purpose so the caller can report instead of hanging)
+  string join(int seconds = 60) {
+    string stuck;
+    for (int tick = 0; tick < seconds * 100; ++tick) {
+      bool all = true;
+      for (auto& s : state) all = all && s->load() == 2;
+      if (all) break;
+      std::this_thread::sleep_for(std::chrono::milliseconds(10));
+    }
+    for (size_t i = 0; i < nodes.size(); ++i)
+      if (state[i]->load() != 2) stuck += nodes[i].id() + (state[i]->load() == 0 ? "(in start) " : "(in stop) ");
+    if (stuck.empty()) {
+      for (auto& t : threads) t.join();
+      offices.clear();
+    } else {
+      for (auto& t : threads) t.detach();
+      for (auto& o : offices) o.release();
+    }
+    return stuck;
   }
 };
 }  // namespace
@@ -589,8 +610,9 @@ PSH_API int psh_run_replace_scenario(int32_t n_keys, float* out_vals, uint64_t* 
   c.offices[c.index("S1")]->kill();
   sched.replaceNode(dead, live);
   gate.set(2);
-  c.join();
+  string stuck = c.join(30);
   FLAGS_num_replicas = saved;
+  if (!stuck.empty()) return fail("nodes did not stop: " + stuck);
   if ((int)got.size() != n_keys) return fail("worker pulled " + to_string(got.size()) + " values");
   for (int i = 0; i < n_keys; ++i) out_vals[i] = got[i];
   return 0;
@@ -615,7 +637,8 @@ PSH_API int psh_run_heartbeat_scenario(int32_t interval_s, int32_t run_ms, int32
   std::this_thread::sleep_for(std::chrono::milliseconds(run_ms * 9 / 10));
   string rep = c.offices[0]->dashboardReport();
   if (n_dead) *n_dead = (int32_t)c.offices[0]->deadNodes(dead_timeout_s).size();
-  c.join();
+  string stuck = c.join(30);
+  if (!stuck.empty()) return fail("nodes did not stop: " + stuck);
   return put(rep, out, cap, len);
 }
 

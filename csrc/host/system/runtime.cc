@@ -131,15 +131,38 @@ int RNode::submit(MessagePtrList& msgs) {
   }
   outgoing_task_.start(t);
   for (size_t i = 0; i < msgs.size(); ++i) {
-    RNodePtr& w = members[i];
+    RNodePtr w = members[i];
+    if (w.get() != this) w->outgoing_task_.start(t);
+    // the member may have been swapped out (Executor::replace) after the group was listed:
+    // data requests go to its replacement, control requests are not waited for
+    RNodePtr successor;
+    bool retired = false;
     {
       Lock l(w->mu_);
-      msgs[i]->recver = w->id();
-      w->time_ = std::max(t, w->time_);
-      w->pending_msgs_[t] = msgs[i];
-      if (msgs[i]->recv_handle) w->msg_receive_handle_[t] = msgs[i]->recv_handle;
+      retired = w->retired_;
+      successor = w->replaced_by_;
+      if (!retired) {
+        msgs[i]->recver = w->id();
+        w->time_ = std::max(t, w->time_);
+        w->pending_msgs_[t] = msgs[i];
+        if (msgs[i]->recv_handle) w->msg_receive_handle_[t] = msgs[i]->recv_handle;
+      }
     }
-    if (w.get() != this) w->outgoing_task_.start(t);
+    if (retired) {
+      if (msgs[i]->task.type() != TaskView::CALL_CUSTOMER || !successor) {
+        w->outgoing_task_.finish(t);
+        continue;
+      }
+      {
+        Lock l(successor->mu_);
+        msgs[i]->recver = successor->id();
+        successor->time_ = std::max(t, successor->time_);
+        successor->pending_msgs_[t] = msgs[i];
+        if (msgs[i]->recv_handle) successor->msg_receive_handle_[t] = msgs[i]->recv_handle;
+      }
+      successor->outgoing_task_.start(t);
+      w = successor;
+    }
     if (msgs[i]->valid) w->encodeFilter(msgs[i]);
     exec_.sys().queue(msgs[i]);
   }
@@ -321,22 +344,37 @@ void Executor::remove(const NodeView& node) {
 }
 
 void Executor::replace(const NodeView& dead, const NodeView& live) {
-  // the live node takes over role, rank and key range of the dead one; requests that were
-  // never answered are re-sent to it with their original timestamps
+  // the live node takes over role, rank and key range of the dead one.  Data requests the dead
+  // node never answered are re-sent to it with their original timestamps, and whoever waits on
+  // the dead node's tracker is released when the replacement answers.  Control requests
+  // (MANAGE: INIT / RUN ...) are not replayed - Postoffice::replaceNode drives the spare through
+  // that sequence itself - they just stop being waited for.
   RNodePtr old = rnode(dead.id());
-  MessagePtrList pending = old ? old->pendingMsgs() : MessagePtrList();
   remove(dead);
   add(live);
   RNodePtr nw = rnode(live.id());
+  nw->replaces_ = old;
+  MessagePtrList pending;
+  if (old) {  // from here on RNode::submit redirects instead of registering on the dead node
+    Lock l(old->mu_);
+    old->retired_ = true;
+    old->replaced_by_ = nw;
+    for (auto& kv : old->pending_msgs_) pending.push_back(kv.second);
+  }
   for (auto& m : pending) {
+    const int t = m->task.time();
+    if (m->task.type() != TaskView::CALL_CUSTOMER) {
+      old->outgoing_task_.finish(t);
+      continue;
+    }
     MessagePtr again(new Message(*m));
     again->recver = live.id();
     {
       Lock l(nw->mu_);
-      nw->pending_msgs_[m->task.time()] = again;
-      nw->time_ = std::max(nw->time_, m->task.time());
+      nw->pending_msgs_[t] = again;
+      nw->time_ = std::max(nw->time_, t);
     }
-    nw->outgoing_task_.start(m->task.time());
+    nw->outgoing_task_.start(t);
     sys_.queue(again);
   }
 }
@@ -440,6 +478,7 @@ void Executor::run() {
         sender->pending_msgs_.erase(it);
       }
       sender->outgoing_task_.finish(t);
+      if (sender->replaces_) sender->replaces_->outgoing_task_.finish(t);
       RNodePtr o = rnode(original);
       if (!o) continue;
       if (o->tryWaitOutgoingTask(t)) {
@@ -946,7 +985,11 @@ void Postoffice::recv() {
             Lock l(mu_);
             (cmd == ManageAppView::INIT ? init_msg_ : run_msg_) = msg;
           }
-          (cmd == ManageAppView::INIT ? init_app_promise_ : run_app_promise_).set_value();
+          try {
+            (cmd == ManageAppView::INIT ? init_app_promise_ : run_app_promise_).set_value();
+          } catch (const std::future_error&) {
+            reply(msg->sender, tk);  // a repeated INIT / RUN: nothing left to do
+          }
           continue;
         }
         manageApp(tk);

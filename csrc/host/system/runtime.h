@@ -115,6 +115,9 @@ class RNode {
   std::mutex mu_;
   int time_ = Message::kInvalidTime;
   TaskTracker incoming_task_, outgoing_task_;
+  shared_ptr<RNode> replaces_;  // the dead node whose unanswered requests were re-sent to me
+  shared_ptr<RNode> replaced_by_;  // set (with retired_, under mu_) when this node was swapped out
+  bool retired_ = false;
   std::map<int, MessagePtr> pending_msgs_;
   std::map<int, Message::Callback> msg_receive_handle_, msg_finish_handle_;
   std::mutex filter_mu_;

