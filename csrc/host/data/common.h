@@ -86,7 +86,9 @@ inline DataConfig searchFiles(const DataConfigView& config) {
     for (const auto& f : readFilenamesInDirectory(dir)) {
       const string name = getFilename(f);
       if (std::regex_match(name, pattern) || name == base) {
-        string l = config.format() == DataConfigView::TEXT ? name : removeExtension(name);
+        // BIN matrices are several files sharing a stem; TEXT and PROTO (RecordIO) are one file each
+        const bool whole = config.format() == DataConfigView::TEXT || config.format() == DataConfigView::PROTO;
+        string l = whole ? name : removeExtension(name);
         matched.push_back(dir.file(0) + "/" + l);
       }
     }

@@ -23,7 +23,9 @@ class SlotReader {
   SlotReader(const DataConfigView& data, const DataConfigView& cache) { init(data, cache); }
 
   void init(const DataConfigView& data, const DataConfigView& cache) {
-    CHECK(data.format() == DataConfigView::TEXT) << "SlotReader reads TEXT data";
+    // TEXT as in the reference (slot_reader.cc:14), plus PROTO: RecordIO files of Example protos
+    CHECK(data.format() == DataConfigView::TEXT || data.format() == DataConfigView::PROTO)
+        << "SlotReader reads TEXT or PROTO data";
     if (cache.file_size()) {
       cache_ = cache.file(0);
       string dir = cache_.back() == '/' ? cache_ : getPath(cache_);
@@ -153,9 +155,7 @@ class SlotReader {
     std::vector<VSlot> vslots(kSlotIDmax);
     uint32 num_ex = 0;
     Example ex;
-    FileLineReader reader(data);
-    reader.set_line_callback([&](char* line) {
-      if (!text_parser.toProto(line, &ex)) return;
+    auto take = [&]() {
       if (!info_parser.add(ex)) return;
       for (const Slot& slot : ex.slot) {
         VSlot& vs = vslots[slot.id];
@@ -165,11 +165,26 @@ class SlotReader {
         vs.row_siz.pushBack((uint16)std::max(slot.key.size(), slot.val.size()));
       }
       ++num_ex;
-    });
-    reader.Reload();
-    if (!reader.loaded_successfully()) {
-      LL << "cannot read " << data.file(0);
-      return false;
+    };
+    if (data.format() == DataConfigView::PROTO) {
+      File* f = File::open(data.file(0), "r");
+      if (!f) {
+        LL << "cannot read " << data.file(0);
+        return false;
+      }
+      RecordReader records(f);
+      while (records.ReadProtocolMessage(&ex)) take();
+      f->close();
+    } else {
+      FileLineReader reader(data);
+      reader.set_line_callback([&](char* line) {
+        if (text_parser.toProto(line, &ex)) take();
+      });
+      reader.Reload();
+      if (!reader.loaded_successfully()) {
+        LL << "cannot read " << data.file(0);
+        return false;
+      }
     }
     info = info_parser.info();
     for (int i = 0; i < kSlotIDmax; ++i) {

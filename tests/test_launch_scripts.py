@@ -64,3 +64,23 @@ def test_mpi_node_sh_ranks_from_environment(tmp_path):
                 p.kill()
     assert all(p.returncode == 0 for p in procs), "\n".join(outs)
     _check_hello("\n".join(outs))
+
+
+def test_text2proto_and_show_example(tmp_path):
+    """text -> RecordIO of Example protos (+ .info); a DataConfig{format: PROTO} reads it back."""
+    from parameter_server_b200.utils.data_io import load_slot_data
+    from parameter_server_b200.utils.synthetic import make_rcv1_like, write_libsvm
+    shard = make_rcv1_like(200, 80, 8.0, seed=5)
+    write_libsvm(shard, str(tmp_path / "a.txt"))
+    r = subprocess.run([str(ROOT / "build" / "text2proto"), "-input", str(tmp_path / "a.txt"), "-format", "libsvm",
+                        "-output", str(tmp_path / "a")], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and "written 200 examples" in r.stderr, r.stderr
+    info = (tmp_path / "a.info").read_text()
+    assert "num_ex: 200" in info and f"nnz_ele: {shard.nnz}" in info
+    r = subprocess.run([str(ROOT / "build" / "show_example"), "-input", str(tmp_path / "a.recordio"), "-n", "2"],
+                       capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and r.stdout.count("example ") == 2 and "slot { id: 0 val:" in r.stdout
+    g = load_slot_data(f'format: PROTO file: "{tmp_path}/a.recordio"', str(tmp_path / "cache_"))[1]
+    assert g.n_rows == 200 and g.nnz == shard.nnz
+    import torch
+    assert torch.equal(g.keys, shard.keys)
