@@ -67,6 +67,29 @@ __global__ void k_kv_lookup_insert(const uint64_t* __restrict__ keys, int64_t n,
   }
 }
 
+// ---- bounded waits -----------------------------------------------------------------------------------
+// A wait on a peer's flag gives up after ~2^21 polls (seconds) instead of hanging the GPU: it
+// records {code, index, wanted, seen} in a host-pinned sink (psb_sgd_set_fault_sink) and lets
+// the kernel run on, so every rank drains and the host can raise.  code 1: worker waiting for
+// an owner's acknowledgement, code 2: server waiting for a worker's push.
+__device__ unsigned long long* g_sgd_fault_sink = nullptr;
+__device__ __forceinline__ void spin_or_fault(const uint64_t* flag, uint64_t want, int code, int index) {
+  uint32_t polls = 0;
+  uint64_t seen;
+  while ((seen = ld_acquire_sys(flag)) < want) {
+    __nanosleep(20);
+    if (++polls > (1u << 21)) {
+      unsigned long long* sink = g_sgd_fault_sink;
+      if (sink && atomicCAS_system(sink, 0ull, (unsigned long long)code) == 0ull) {
+        sink[1] = (unsigned long long)index;
+        sink[2] = want;
+        sink[3] = seen;
+      }
+      return;
+    }
+  }
+}
+
 // ---- worker step -------------------------------------------------------------------------------------
 typedef psb_sgd_worker SgdWorker;
 typedef psb_sgd_server SgdServer;
@@ -142,7 +165,7 @@ k_sgd_worker_step(const __grid_constant__ SgdWorker W, uint64_t seq, uint32_t* b
   if (W.n_workers > 1 || W.depth > 1) {
     // the region is free once the owner acknowledged push seq - depth
     if (threadIdx.x < W.n_servers && seq > (uint64_t)W.depth)
-      spin_until_ge(W.ack + threadIdx.x, seq - (uint64_t)W.depth);
+      spin_or_fault(W.ack + threadIdx.x, seq - (uint64_t)W.depth, 1, W.rank * 100 + threadIdx.x);
     __syncthreads();
   }
   for (int s = 0; s < W.n_servers; ++s) {
@@ -212,7 +235,7 @@ k_sgd_server(const __grid_constant__ SgdServer S, int wkr, uint64_t seq) {
   __shared__ double sh[3][kSgdWarps];
   const int64_t gt = (int64_t)blockIdx.x * kSgdThreads + threadIdx.x, nt = (int64_t)gridDim.x * kSgdThreads;
   double d_nnz = 0, d_w2 = 0, d_d2 = 0;
-  if (threadIdx.x == 0) spin_until_ge(S.land_flag + wkr, seq);
+  if (threadIdx.x == 0) spin_or_fault(S.land_flag + wkr, seq, 2, S.rank * 100 + wkr);
   __syncthreads();
   const int64_t region = (int64_t)(seq % (uint64_t)S.depth);
   const int64_t n = __ldcg(S.land_cnt + (int64_t)wkr * S.depth + region);
@@ -322,6 +345,13 @@ PSB_API int psb_kv_lookup_insert(const uint64_t* keys, int64_t n, const int32_t*
   }
   k_kv_lookup_insert<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(keys, n, owner, T, slot_out, overflow_dev);
   PSB_LAUNCH_CHECK();
+  return 0;
+}
+
+// `host_pinned`: 4 zeroed uint64 in pinned (mapped) host memory, or NULL to disable
+PSB_API int psb_sgd_set_fault_sink(uint64_t* host_pinned) {
+  unsigned long long* p = reinterpret_cast<unsigned long long*>(host_pinned);
+  PSB_CUDA(cudaMemcpyToSymbol(g_sgd_fault_sink, &p, sizeof(p)));
   return 0;
 }
 

@@ -266,6 +266,9 @@ int psb_kv_export_nonzero(const uint64_t* keys, const float* w, int64_t cap, uin
                           float* out_w, uint64_t* count_dev, void* stream);
 /* K6+K7+C3+C4: pull, margins / loss / gradient, push of one minibatch in one cooperative launch.
  * `bar`: one zeroed uint32.  seq starts at 1 and increases by one per step. */
+/* Waits on peer flags give up after seconds and record {code, index, wanted, seen} here
+ * (4 zeroed uint64 in pinned host memory; NULL disables) instead of hanging the GPU. */
+int psb_sgd_set_fault_sink(uint64_t* host_pinned);
 int psb_sgd_max_grid(void);
 int psb_sgd_worker_step(const psb_sgd_worker* wk, uint64_t seq, int32_t grid, uint32_t* bar,
                         void* stream);

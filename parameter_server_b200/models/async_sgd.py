@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 import sys
 import time
 from dataclasses import dataclass
@@ -119,6 +120,7 @@ def _lib():
         lib.psb_sgd_worker_step.argtypes = [P, C.c_uint64, C.c_int32, P, P]
         lib.psb_sgd_server_update.argtypes = [P, C.c_uint64, C.c_int32, P]
         lib.psb_sgd_max_grid.restype = C.c_int
+        lib.psb_sgd_set_fault_sink.argtypes = [P]
         lib._sgd_sigs = True
     return lib
 
@@ -179,6 +181,9 @@ class AsyncSGDEngine:
         self.bar = torch.zeros(4, dtype=torch.int32, device=dev)
         self.overflow = torch.zeros(1, dtype=torch.int32, device=dev)
         self.grid = int(self.lib.psb_sgd_max_grid())
+        # device waits that time out report here instead of hanging the GPU (sgd.cu spin_or_fault)
+        self.fault = torch.zeros(4, dtype=torch.int64).pin_memory()
+        check(self.lib.psb_sgd_set_fault_sink(self.fault.data_ptr()))
         sm = torch.cuda.get_device_properties(dev).multi_processor_count
         self.grid_server = sm * 2
         whole = Range.all()
@@ -212,6 +217,14 @@ class AsyncSGDEngine:
         if mb in self._cache:
             return self._cache[mb]
         cfg, dev, d = self.cfg, self.device, self.data
+        trace = os.environ.get("PSB_SGD_TRACE")
+
+        def mark(what):
+            if trace:
+                torch.cuda.synchronize(dev)
+                print(f"[trace] rank {self.rank} mb {mb} seq {self.seq} {what} t={time.time() % 1000:.3f}",
+                      file=sys.stderr, flush=True)
+        mark("prepare begin (previous step drained)")
         a = min(mb * cfg.minibatch, self.n_rows)
         b = min(a + cfg.minibatch, self.n_rows)
         lo, hi = int(d.row_ptr[a].item()), int(d.row_ptr[b].item())
@@ -220,6 +233,7 @@ class AsyncSGDEngine:
         if cfg.tail_feature_freq > 0 and hi > lo:
             uniq = uniq[cnt > cfg.tail_feature_freq].contiguous()
         n_cols = uniq.numel()
+        mark(f"unique done n_cols={n_cols}")
         idx1 = L.lookup_sorted(uniq, keys_nnz) if hi > lo else torch.empty(0, dtype=torch.int32, device=dev)
         row_ptr = (d.row_ptr[a:b + 1] - lo).contiguous()
         vals = d.vals[lo:hi].contiguous() if d.vals is not None else None
@@ -241,6 +255,10 @@ class AsyncSGDEngine:
             check(self.lib.psb_kv_lookup_insert(ptr(uniq), n_cols, ptr(col_owner), self.tab_keys_ptrs,
                                                 self.tab_caps, W, ptr(col_slot), ptr(self.overflow),
                                                 current_stream()))
+        mark("lookup_insert done")
+        self._new_minibatches = getattr(self, "_new_minibatches", 0) + 1
+        if self._new_minibatches % 8 == 0:
+            self.check_table_load()
         m = _Minibatch(rp, col, val, d.y[a:b].contiguous(), uniq, col_owner, col_slot, owner_begin,
                        b - a, n_cols)
         self._cache[mb] = m
@@ -292,10 +310,33 @@ class AsyncSGDEngine:
                                              current_stream()))
         self.launches += 1 + self.world
 
+    def check_table_load(self) -> float:
+        """Open addressing with linear probing degrades sharply when a shard's table fills up
+        (probe chains of thousands, each probe a peer round trip for remote workers): refuse to
+        crawl.  Returns the load factor of this rank's shard."""
+        if int(self.overflow.item()):
+            raise RuntimeError(f"rank {self.rank}: a shard's key table is full (table_capacity="
+                               f"{self.cfg.table_capacity}); raise AsyncSGDConfig.table_capacity")
+        used = int((self.b_keys.tensor != -1).sum().item())
+        load = used / self.cfg.table_capacity
+        if load > 0.75:
+            raise RuntimeError(f"rank {self.rank}: key table {load:.0%} full ({used} of {self.cfg.table_capacity} "
+                               "slots); raise AsyncSGDConfig.table_capacity to at least twice the keys of a shard")
+        return load
+
+    def check_fault(self) -> None:
+        """Raise if a device-side wait on a peer's flag timed out (the run is invalid from there)."""
+        if int(self.fault[0]) != 0:
+            code, idx, want, seen = (int(x) for x in self.fault.tolist())
+            what = {1: "worker waiting for an owner's acknowledgement", 2: "server waiting for a worker's push"}
+            raise RuntimeError(f"rank {self.rank}: device wait timed out: {what.get(code, code)} "
+                               f"(rank {idx // 100}, peer {idx % 100}) wanted seq {want}, saw {seen}")
+
     def step(self, mb: int):
         """One minibatch: worker kernel, then this rank's server applies every worker's push."""
         m = self.worker_step(mb)
         self.server_step()
+        self.check_fault()
         return m
 
     def train(self, verbose: bool = True) -> list:

@@ -119,7 +119,7 @@ def make_ctr_like(n_rows: int, n_groups: int = 8, keys_per_group: int = 1 << 20,
         row = torch.div(comb, keys_per_group, rounding_mode="floor")
         rank = comb - row * keys_per_group
         # multiplicative hash into 54 bits, group id in the top 10 bits
-        h = (rank * (0x9E3779B97F4A7C15 - (1 << 64)) + grp * 0x632BE59BD9B4E019) & ((1 << 54) - 1)
+        h = (rank * (0x9E3779B97F4A7C15 - (1 << 64)) + ((grp * 0x632BE59BD9B4E019) & ((1 << 54) - 1))) & ((1 << 54) - 1)
         keys = h | (grp << 54)
         wg = _planted_model(keys_per_group, seed + grp, density=0.01, device=dev)
         margin.index_add_(0, row, wg[rank])
