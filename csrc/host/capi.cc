@@ -642,6 +642,127 @@ PSH_API int psh_run_heartbeat_scenario(int32_t interval_s, int32_t run_ms, int32
   return put(rep, out, cap, len);
 }
 
+// ---- van ring / key-range reassignment (ref src/test/van_test.cc, reassign_server_key_range.cc) -------
+// n vans in one process; a message with a key array and a value array of `payload` elements goes
+// around the ring n times (every van forwards what it receives to its successor).  Returns 0 when
+// the payload arrives intact at node 0; *bytes = what node 0 sent.
+PSH_API int psh_van_ring(int32_t n, int32_t use_tcp, int32_t base_port, int32_t payload, int64_t* bytes) {
+  if (n < 2) return fail("ring needs at least 2 nodes");
+  auto fabric = std::make_shared<InprocFabric>();
+  std::vector<Node> nodes(n);
+  std::vector<unique_ptr<Van>> vans(n);
+  for (int i = 0; i < n; ++i) {
+    nodes[i].set_role(NodeView::WORKER);
+    nodes[i].set_id("N" + to_string(i));
+    nodes[i].set_hostname("127.0.0.1");
+    nodes[i].set_port(base_port + i);
+    if (use_tcp) vans[i].reset(new TcpVan());
+    else vans[i].reset(new InprocVan(fabric));
+    if (!vans[i]->init(nodes[i])) return fail("van init failed for " + nodes[i].id());
+  }
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j < n; ++j)
+      if (i != j && !vans[i]->connect(nodes[j])) return fail("connect failed");
+  SArray<Key> key(payload);
+  SArray<float> val(payload);
+  for (int i = 0; i < payload; ++i) { key[i] = (Key)i * 7919u; val[i] = 0.5f * i; }
+  const int laps = n;
+  std::atomic<int> errors(0);
+  std::vector<std::thread> th;
+  for (int i = 1; i < n; ++i) {
+    th.emplace_back([&, i] {
+      for (int lap = 0; lap < laps; ++lap) {
+        MessagePtr m;
+        size_t b = 0;
+        if (!vans[i]->recv(&m, &b).ok()) { ++errors; return; }
+        m->sender = nodes[i].id();
+        m->recver = nodes[(i + 1) % n].id();
+        if (!vans[i]->send(m, &b).ok()) { ++errors; return; }
+      }
+    });
+  }
+  MessagePtr cur(new Message());
+  cur->task.set_type(TaskView::CALL_CUSTOMER);
+  cur->task.set_customer("ring");
+  cur->setKey(key);
+  cur->addValue(val);
+  size_t sent = 0;
+  for (int lap = 0; lap < laps; ++lap) {
+    cur->sender = nodes[0].id();
+    cur->recver = nodes[1].id();
+    size_t b = 0;
+    if (!vans[0]->send(cur, &b).ok()) return fail("send failed");
+    sent += b;
+    MessagePtr back;
+    if (!vans[0]->recv(&back, &b).ok()) return fail("recv failed");
+    cur = back;
+  }
+  for (auto& t : th) t.join();
+  for (auto& v : vans) v->shutdown();
+  if (bytes) *bytes = (int64_t)sent;
+  if (errors) return fail("a ring member failed");
+  SArray<Key> k2(cur->key);
+  if (cur->value.size() != 1) return fail("value array lost");
+  SArray<float> v2(cur->value[0]);
+  if (k2.size() != (size_t)payload || v2.size() != (size_t)payload) return fail("payload size changed");
+  for (int i = 0; i < payload; ++i)
+    if (k2[i] != key[i] || v2[i] != val[i]) return fail("payload corrupted at " + to_string(i));
+  if (cur->task.customer() != "ring") return fail("task header lost");
+  return 0;
+}
+
+namespace {
+// scheduler: repartition the servers' key ranges inside [lo, hi) and broadcast ManageNode::UPDATE
+class ReassignRoot : public App {
+ public:
+  ReassignRoot(const string& name, Key lo, Key hi) : App(name), lo_(lo), hi_(hi) {}
+  void init() override {
+    auto nodes = Postmaster::partitionServerKeyRange(sys_.yp().nodes(), Range<Key>(lo_, hi_));
+    Task task;
+    task.set_type(TaskView::MANAGE);
+    task.mutable_mng_node().set_cmd(ManageNodeView::UPDATE);
+    for (const auto& n : nodes) task.mutable_mng_node().add_node().raw()->copyFrom(*n.raw());
+    port(kLiveGroup)->submitAndWait(task);
+  }
+  Key lo_, hi_;
+};
+class ReassignSlave : public App {
+ public:
+  ReassignSlave(const string& name, std::map<string, std::pair<Key, Key>>* out, std::mutex* mu)
+      : App(name), out_(out), mu_(mu) {}
+  void run() override {
+    Range<Key> r = myKeyRange();
+    Lock l(*mu_);
+    (*out_)[myNodeID()] = std::make_pair(r.begin(), r.end());
+  }
+  std::map<string, std::pair<Key, Key>>* out_;
+  std::mutex* mu_;
+};
+}  // namespace
+
+// every node's key range as it sees it in run(), after the scheduler reassigned [lo, hi) in init():
+// lines "<id> <begin> <end>"
+PSH_API int psh_run_reassign_scenario(int32_t num_servers, int32_t num_workers, uint64_t lo, uint64_t hi,
+                                      char* out, int64_t cap, int64_t* len) {
+  std::map<string, std::pair<Key, Key>> got;
+  std::mutex mu;
+  MiniCluster c;
+  c.add(NodeView::SCHEDULER, "H");
+  for (int i = 0; i < num_servers; ++i) c.add(NodeView::SERVER, "S" + to_string(i));
+  for (int i = 0; i < num_workers; ++i) c.add(NodeView::WORKER, "W" + to_string(i));
+  auto factory = [&](const string& name, const string&) -> App* {
+    NodeView me = Postoffice::current().myNode();
+    if (me.role() == NodeView::SCHEDULER) return new ReassignRoot(name, lo, hi);
+    return new ReassignSlave(name, &got, &mu);
+  };
+  c.launch(num_servers, num_workers, 0, 0, factory);
+  string stuck = c.join(30);
+  if (!stuck.empty()) return fail("nodes did not stop: " + stuck);
+  std::ostringstream os;
+  for (const auto& kv : got) os << kv.first << " " << kv.second.first << " " << kv.second.second << "\n";
+  return put(os.str(), out, cap, len);
+}
+
 // ---- diagnostics ---------------------------------------------------------------------------------------
 #include <execinfo.h>
 #include <signal.h>

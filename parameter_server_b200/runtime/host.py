@@ -234,3 +234,22 @@ def run_heartbeat_scenario(interval_s: int = 1, run_ms: int = 2600, dead_timeout
     hcheck(_lib().psh_run_heartbeat_scenario(interval_s, run_ms, dead_timeout_s, buf, 1 << 16, C.byref(n),
                                              C.byref(dead)))
     return buf.raw[:n.value].decode(), int(dead.value)
+
+
+def van_ring(n: int = 3, tcp: bool = True, base_port: int = 9600, payload: int = 1000) -> int:
+    """A message with `payload` keys and values travels n laps around a ring of n vans
+    (ref src/test/van_test.cc); returns the bytes node 0 sent."""
+    b = C.c_int64(0)
+    hcheck(_lib().psh_van_ring(n, int(tcp), base_port, payload, C.byref(b)))
+    return int(b.value)
+
+
+def run_reassign_scenario(num_servers: int, num_workers: int, lo: int, hi: int) -> dict:
+    """{node id: (begin, end)} after the scheduler re-partitioned [lo, hi) over the servers and
+    broadcast ManageNode::UPDATE (ref src/test/reassign_server_key_range.cc)."""
+    text = _str_out(_lib().psh_run_reassign_scenario, num_servers, num_workers, C.c_uint64(lo), C.c_uint64(hi))
+    out = {}
+    for line in text.strip().splitlines():
+        i, b, e = line.split()
+        out[i] = (int(b), int(e))
+    return out

@@ -159,3 +159,21 @@ def test_kv_cluster_inproc_and_tcp():
     assert np.allclose(got, want)
     got = host.run_kv_cluster(3, 2, 6, [0, 2, 4, 5], tcp=True, base_port=19200 + os.getpid() % 500)
     assert np.allclose(got, want)
+
+
+@pytest.mark.parametrize("tcp", [False, True])
+def test_van_ring(tcp):
+    """ref src/test/van_test.cc: a message survives n laps around a ring of vans unchanged"""
+    sent = host.van_ring(4, tcp=tcp, base_port=21000 + os.getpid() % 3000, payload=5000)
+    assert sent >= 4 * 5000 * (8 + 4)          # 4 laps of keys + values leave node 0
+
+
+def test_reassign_server_key_range():
+    """ref src/test/reassign_server_key_range.cc: ManageNode::UPDATE re-partitions [0, 100)"""
+    from parameter_server_b200.utils.range import Range
+    got = host.run_reassign_scenario(3, 3, 0, 100)
+    assert sorted(got) == ["S0", "S1", "S2", "W0", "W1", "W2"]
+    for s in range(3):
+        r = Range(0, 100).even_divide(3, s)
+        assert got[f"S{s}"] == (r.begin, r.end)
+    assert all(got[f"W{w}"] == (0, 100) for w in range(3))
