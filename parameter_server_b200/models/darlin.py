@@ -43,6 +43,11 @@ class DarlinConfig:
     random_feature_block_order: bool = True
     max_block_delay: int = 0          # tau
     tail_feature_freq: int = 0
+    countmin_k: int = 2               # bcd.proto:30
+    countmin_n_ratio: float = 2.0     # bcd.proto:32
+    tail_filter: str = "exact"        # "exact": true global counts (device sort + RLE);
+    #                                   "countmin": the reference's sketch (may keep a few rare
+    #                                   features because of hash collisions), same hash as the host
     prior_fea_group: list = field(default_factory=list)
     num_iter_for_prior_fea_group: int = 5
     delta_init_value: float = 1.0
@@ -75,7 +80,7 @@ class DarlinConfig:
         if d is not None:
             for name in ("max_pass_of_data", "epsilon", "feature_block_ratio",
                          "random_feature_block_order", "max_block_delay", "tail_feature_freq",
-                         "num_iter_for_prior_fea_group"):
+                         "num_iter_for_prior_fea_group", "countmin_k", "countmin_n_ratio"):
                 v = d.get(name)
                 if v is not None:
                     setattr(c, name, type(getattr(c, name))(v))
@@ -146,7 +151,16 @@ class DarlinEngine:
             cparts = self.comm.gather_var(cnt)
             allk = torch.cat(parts) if W > 1 else uniq
             dictionary = L.unique_count(allk)[0] if W > 1 else uniq
-            if cfg.tail_feature_freq > 0:
+            if cfg.tail_feature_freq > 0 and cfg.tail_filter == "countmin":
+                # ref darlin.h:62-75 + kv_vector.h tail filter: every worker inserts its (key, count)
+                # pairs into the owners' sketch, then asks which of its keys occur often enough
+                from ..ops.evaluation import CountMin
+                n = int(max(p.numel() for p in parts) * W * cfg.countmin_n_ratio)
+                cm = CountMin(n, cfg.countmin_k, dev)
+                for p, c in zip(parts, cparts):
+                    cm.insert(p, c.clamp(max=255))
+                dictionary = dictionary[cm.query_gt(dictionary, cfg.tail_feature_freq)].contiguous()
+            elif cfg.tail_feature_freq > 0:
                 total = torch.zeros(dictionary.numel(), dtype=torch.int64, device=dev)
                 for p, c in zip(parts, cparts):
                     idx = L.lookup_sorted(dictionary, p).long() - 1

@@ -144,3 +144,20 @@ def test_darlin_graph_train_decreases_objective(tmp_path):
     m = read_model_text([path])
     assert len(m) == prog[-1].nnz_w
     e.close()
+
+
+def test_darlin_countmin_tail_filter_is_superset_of_exact():
+    """tail_filter="countmin" (the reference's sketch) never drops a feature the exact count keeps."""
+    from parameter_server_b200.models.darlin import DarlinConfig, DarlinEngine
+    from parameter_server_b200.utils.synthetic import make_rcv1_like
+    dev = torch.device("cuda:0")
+    data = make_rcv1_like(3000, 4000, 12.0, seed=9, device=dev)
+    dicts = {}
+    for mode in ("exact", "countmin"):
+        eng = DarlinEngine(DarlinConfig(tail_feature_freq=3, tail_filter=mode, countmin_k=2), None, dev)
+        eng.load(data)
+        dicts[mode] = set(eng.keys_all.tolist())
+        eng.close()
+    assert dicts["exact"] <= dicts["countmin"]
+    extra = len(dicts["countmin"]) - len(dicts["exact"])
+    assert 0 < len(dicts["exact"]) < 4000 and extra <= 0.05 * len(dicts["exact"]) + 5
