@@ -119,6 +119,18 @@ k_sgd_worker_step(const __grid_constant__ SgdWorker W, uint64_t seq, uint32_t* b
   const int64_t gw = (int64_t)blockIdx.x * kSgdWarps + wid, nw = (int64_t)gridDim.x * kSgdWarps;
   const uint32_t G = gridDim.x;
 
+  // Bounded delay (ref linear.proto:47 max_delay): minibatch `seq` may start only when every
+  // owner has applied ALL workers' pushes up to seq - depth (depth = max_delay + 1).  The
+  // acknowledgement also frees ring region seq % depth for this step's push.  Waiting here, before
+  // the pull, bounds the staleness of the pulled weights from below; it does not bound it from
+  // above: an owner applies a push as soon as it arrives, so a slower worker may already see part
+  // of step `seq` (asynchronous SGD, as in the reference - not sequentially consistent).
+  if (W.n_workers > 1 || W.depth > 1) {
+    if (threadIdx.x < W.n_servers && seq > (uint64_t)W.depth)
+      spin_or_fault(W.ack + threadIdx.x, seq - (uint64_t)W.depth, 1, W.rank * 100 + threadIdx.x);
+    __syncthreads();
+  }
+
   // ---- phase 1: pull the weights of this minibatch's columns from their owners ----
   for (int64_t j = gt; j < W.n_cols; j += nt) {
     const int64_t s = W.col_slot[j];
@@ -162,12 +174,6 @@ k_sgd_worker_step(const __grid_constant__ SgdWorker W, uint64_t seq, uint32_t* b
   // ---- phase 3: push every owner's segment into region seq % depth of its ring ----
   const int64_t region = (int64_t)(seq % (uint64_t)W.depth);
   const int64_t sblk = W.land_cap / kQuantBlock + 1;
-  if (W.n_workers > 1 || W.depth > 1) {
-    // the region is free once the owner acknowledged push seq - depth
-    if (threadIdx.x < W.n_servers && seq > (uint64_t)W.depth)
-      spin_or_fault(W.ack + threadIdx.x, seq - (uint64_t)W.depth, 1, W.rank * 100 + threadIdx.x);
-    __syncthreads();
-  }
   for (int s = 0; s < W.n_servers; ++s) {
     const int64_t lo = W.owner_begin[s], hi = W.owner_begin[s + 1];
     const int64_t n = hi - lo;

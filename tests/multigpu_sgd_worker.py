@@ -1,0 +1,112 @@
+"""torchrun worker: async SGD (FTRL, max_delay 0 and 2) on WORLD_SIZE GPUs against the lock-step
+emulation done by rank 0 alone.  The real run is asynchronous: an owner applies a push as soon as it
+arrives, so a slower worker may pull weights that already contain part of the current step.  The two
+runs therefore agree closely (same loss trajectory to ~1e-3, weights to a few 1e-2), not bitwise."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+
+def main():
+    from parameter_server_b200.models.async_sgd import AsyncSGDConfig, AsyncSGDEngine
+    from parameter_server_b200.parallel.comm import TorchComm, run_threads
+    from parameter_server_b200.utils.synthetic import make_rcv1_like
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device(f"cuda:{local}")
+    dist.init_process_group("nccl", device_id=dev)
+    steps = 10
+
+    def shard(r):
+        s = make_rcv1_like(steps * 256, 3000, 24.0, seed=4, shard=r, device=dev)
+        s.keys = (s.keys * ((1 << 63) // 3000 * 2)).contiguous()   # every shard owns some keys
+        return s
+
+    dup = [0]
+
+    def model_of(e):
+        k, w = e.shard_model()
+        allk = e.b_keys.tensor[e.b_keys.tensor != -1]
+        dup[0] += int(allk.numel() - torch.unique(allk).numel())   # one key in two slots?
+        return dict(zip(k.tolist(), w.tolist()))
+
+    out = {"ok": True}
+    for tau in (0, 2):
+        cfg = AsyncSGDConfig(algo="FTRL", minibatch=256, alpha=0.5, beta=1.0, lambda_l1=0.02, lambda_l2=0.01,
+                             max_delay=tau, table_capacity=1 << 14)
+        eng = AsyncSGDEngine(cfg, TorchComm(), dev, out=open(os.devnull, "w"))
+        eng.load(shard(rank))
+        traj = []
+        for i in range(steps):
+            eng.step(i)
+            torch.cuda.synchronize()
+            st = eng.wstats.clone()
+            eng.wstats.zero_()
+            dist.all_reduce(st)
+            traj.append(round(st[0].item() / max(st[2].item(), 1), 7))
+        eng.check_fault()
+        mine = model_of(eng)
+        dups = [None] * world
+        dist.all_gather_object(dups, dup[0])
+        out[f"duplicate_slots_tau{tau}"] = dups
+        models = [None] * world
+        dist.all_gather_object(models, mine)
+        loss = [sum(traj[-3:]) / 3, 0, 1]
+        eng.close()
+        if rank == 0:
+            multi = {}
+            for m in models:
+                multi.update(m)
+            if tau == 0:
+                shards = [shard(r) for r in range(world)]
+
+                def build(comm):
+                    e = AsyncSGDEngine(cfg, comm, dev, out=open(os.devnull, "w"))
+                    e.load(shards[comm.rank])
+                    return e
+                engines = run_threads(world, build)
+                rtraj = []
+                for i in range(steps):
+                    for e in engines:
+                        e.worker_step(i)
+                    for e in engines:
+                        e.server_step()
+                    torch.cuda.synchronize()
+                    tot = sum(e.wstats[0].item() for e in engines)
+                    rows = sum(e.wstats[2].item() for e in engines)
+                    for e in engines:
+                        e.wstats.zero_()
+                    rtraj.append(round(tot / max(rows, 1), 7))
+                out["loss_multi"], out["loss_emulated"] = traj, rtraj
+                ref = {}
+                for e in engines:
+                    ref.update(model_of(e))
+                    e.close()
+                same_keys = set(ref) == set(multi)
+                err = max((abs(ref[k] - multi.get(k, 0.0)) for k in ref), default=0.0)
+                diffs = sorted(((abs(ref.get(k, 0.0) - multi.get(k, 0.0)), k) for k in set(ref) | set(multi)),
+                               reverse=True)
+                out["tau0"] = {"nnz": len(multi), "ref_nnz": len(ref), "same_keys": same_keys, "max_abs_err": err,
+                               "n_diff_1e-4": sum(1 for d, _ in diffs if d > 1e-4),
+                               "n_diff_1e-6": sum(1 for d, _ in diffs if d > 1e-6),
+                               "top": [(round(d, 6), "owner1" if k < 0 else "owner0", round(ref.get(k, 0.0), 4))
+                                       for d, k in diffs[:6]]}
+                gap = max(abs(a - b) for a, b in zip(traj, rtraj))
+                out["tau0"]["max_loss_gap"] = gap
+                out["ok"] &= (traj[0] == rtraj[0] and gap < 5e-3 and err < 0.1 and len(multi) > 100
+                              and abs(len(multi) - len(ref)) <= 20 and sum(dups) == 0)
+            else:
+                out["tau2"] = {"nnz": len(multi), "mean_loss": loss[0] / max(loss[2], 1)}
+                out["ok"] &= len(multi) > 100 and loss[0] / max(loss[2], 1) < 0.6 and sum(dups) == 0
+    dist.barrier()
+    if rank == 0:
+        print(json.dumps(out))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -27,3 +27,16 @@ def test_bench_multi_gpu_matches_emulation(n):
     line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
     res = json.loads(line)
     assert res["ok"], res
+
+
+@pytest.mark.parametrize("n", [2])
+def test_async_sgd_multi_gpu(n):
+    """async SGD over CUDA-IPC peer memory: max_delay 0 tracks the lock-step emulation (closely,
+    not bitwise: owners apply pushes as they arrive), max_delay 2 (ring of 3 landing regions)
+    learns; no device wait times out, no key ends up in two table slots."""
+    if torch.cuda.device_count() < n:
+        pytest.skip("not enough GPUs")
+    r = _torchrun(n, ["tests/multigpu_sgd_worker.py"], timeout=300)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    res = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert res["ok"], res
