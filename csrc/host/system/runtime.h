@@ -226,6 +226,13 @@ class App : public Customer {
   static void setFactory(const Factory& f);
 };
 
+// ---- Engine (ref system.h:4-17): a named customer with no behaviour, kept as an extension point ----
+class Engine : public Customer {
+ public:
+  explicit Engine(const string& name) : Customer(name) {}
+  virtual ~Engine() {}
+};
+
 // ---- YellowPages (ref yellow_pages.{h,cc}) -----------------------------------------------------------
 class YellowPages {
  public:
