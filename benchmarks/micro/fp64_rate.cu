@@ -1,5 +1,5 @@
 // Measures fp64 FMA latency / throughput and the cost of exp() + reciprocal on one SM-ful of warps.
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o build/fp64_rate benchmarks/micro/fp64_rate.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o build/micro/fp64_rate benchmarks/micro/fp64_rate.cu
 #include <cstdio>
 #include <cuda_runtime.h>
 template <int ILP>

@@ -1,6 +1,6 @@
 // What one Darlin step costs in random fp64 traffic alone: W warps, each with 4 independent
 // 8-byte gathers per lane in flight (then a dependent use), and the same shape as fp64 RED.
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o benchmarks/micro/gather_red benchmarks/micro/gather_red.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o build/micro/gather_red benchmarks/micro/gather_red.cu
 #include <cstdio>
 #include <cstdint>
 #include <vector>

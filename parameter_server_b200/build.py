@@ -112,8 +112,22 @@ def build_host(force: bool = False, verbose: bool = False) -> Path | None:
     return out
 
 
+def build_micro(force: bool = False, verbose: bool = False) -> list:
+    """Stand-alone micro-benchmarks (benchmarks/micro/*.cu -> build/micro/<name>), sm_100a."""
+    out = []
+    (BINDIR / "micro").mkdir(parents=True, exist_ok=True)
+    for s in sorted((ROOT / "benchmarks" / "micro").glob("*.cu")):
+        exe = BINDIR / "micro" / s.stem
+        if force or _newer(s, exe, []):
+            _run([_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+                  "-o", str(exe), str(s)], None, verbose)
+        out.append(exe)
+    return out
+
+
 def build_all(force: bool = False, verbose: bool = False) -> dict:
-    return {"cuda": build_cuda(force, verbose), "host": build_host(force, verbose)}
+    return {"cuda": build_cuda(force, verbose), "host": build_host(force, verbose),
+            "micro": build_micro(force, verbose)}
 
 
 if __name__ == "__main__":
