@@ -763,6 +763,188 @@ PSH_API int psh_run_reassign_scenario(int32_t num_servers, int32_t num_workers, 
   return put(os.str(), out, cap, len);
 }
 
+// ---- native unit checks (ref src/test/{bitmap,shared_array,sparse_matrix,localizer,common}_test.cc) --------
+// Runs the C++-side checks of one area ("bitmap", "sarray", "matrix", "localizer", "match", "concurrent")
+// or "all"; returns 0 and an empty message when every check holds, else the first failure.
+namespace {
+struct Checks {
+  std::ostringstream err;
+  int n = 0;
+  void expect(bool ok, const char* what, int line) {
+    ++n;
+    if (!ok && err.str().empty()) err << what << " (capi.cc:" << line << ")";
+  }
+};
+#define EXPECT(c) ck.expect((c), #c, __LINE__)
+
+void checkBitmap(Checks& ck) {
+  Bitmap b(100);
+  EXPECT(b.size() == 100 && b.nnz() == 0);
+  for (uint32 i = 0; i < 100; i += 3) b.set(i);
+  EXPECT(b.nnz() == 34 && b.test(99) && !b.test(98) && b[0]);
+  b.clear(0);
+  EXPECT(!b[0] && b.nnz() == 33);
+  b.fill(true);
+  EXPECT(b.nnz() == 100);       // bits beyond size() stay clear
+  b.resize(33, true);
+  EXPECT(b.nnz() == 33 && b.memSize() == 8);
+}
+
+void checkSArray(Checks& ck) {
+  SArray<int> a = {1, 3, 5, 7, 9, 11};
+  SArray<int> b = {3, 4, 5, 6, 11, 20};
+  EXPECT((a.setIntersection(b) == SArray<int>({3, 5, 11})));
+  EXPECT((a.setUnion(b) == SArray<int>({1, 3, 4, 5, 6, 7, 9, 11, 20})));
+  SArray<int> seg = a.segment(SizeR(1, 4));
+  EXPECT(seg.size() == 3 && seg[0] == 3 && seg[2] == 7);
+  seg[0] = 33;                                   // zero-copy view
+  EXPECT(a[1] == 33);
+  a[1] = 3;
+  SizeR r = a.findRange(Range<int>(4, 10));
+  EXPECT(r.begin() == 2 && r.end() == 5);
+  SArray<double> d(1000);
+  for (size_t i = 0; i < d.size(); ++i) d[i] = (i % 7) * 0.5;
+  SArray<char> z = d.compressTo();
+  SArray<double> e;
+  e.uncompressFrom(z.data(), z.size());
+  EXPECT(e == d && z.size() < d.size() * sizeof(double));
+  SArray<uint64> bits(d);                        // constructing from another element type
+  EXPECT(bits.size() == d.size() && bits[0] == 0);  // reinterprets the same bytes (ref _inl.h:73-80)
+  SArray<char> raw(d);                           // shares memory
+  EXPECT(raw.size() == d.size() * sizeof(double));
+  EXPECT(d.nnz() == 1000 - 143);
+  SArray<int> g;
+  g.pushBack(4); g.pushBack(5); g.append(SArray<int>({6, 7}));
+  EXPECT(g.size() == 4 && g.back() == 7 && g.front() == 4);
+}
+
+void checkMatrix(Checks& ck) {
+  // 3 x 4 CSR:  [1 0 2 0; 0 3 0 0; 4 0 5 6]
+  MatrixInfo info;
+  info.set_type(MatrixInfoView::SPARSE);
+  info.set_row_major(true);
+  info.mutable_row().set_begin(0); info.mutable_row().set_end(3);
+  info.mutable_col().set_begin(0); info.mutable_col().set_end(4);
+  info.set_nnz(6); info.set_sizeof_index(4); info.set_sizeof_value(8);
+  SArray<size_t> off = {0, 2, 3, 6};
+  SArray<uint32> idx = {0, 2, 1, 0, 2, 3};
+  SArray<double> val = {1, 2, 3, 4, 5, 6};
+  MatrixPtr<double> X(new SparseMatrix<uint32, double>(info, off, idx, val));
+  SArray<double> x = {1, 2, 3, 4};
+  EXPECT((X->times(x) == SArray<double>({7, 6, 43})));
+  SArray<double> y = {1, 1, 1};
+  EXPECT((X->transTimes(y) == SArray<double>({5, 3, 7, 6})));
+  MatrixPtr<double> C = X->toColMajor();
+  EXPECT(C && C->colMajor() && (C->times(x) == SArray<double>({7, 6, 43})));
+  EXPECT((C->transTimes(y) == SArray<double>({5, 3, 7, 6})));
+  MatrixPtr<double> blk = C->colBlock(SizeR(2, 4));
+  EXPECT(blk->cols() == 2 && (blk->times(SArray<double>({3, 4})) == SArray<double>({6, 0, 39})));
+  MatrixPtr<double> rows = X->rowBlock(SizeR(1, 3));
+  EXPECT(rows->rows() == 2 && (rows->times(x) == SArray<double>({6, 43})));
+  MatrixPtr<double> sq = X->dotTimes(X);
+  EXPECT((sq->times(SArray<double>({1, 1, 1, 1})) == SArray<double>({5, 9, 77})));
+  DenseMatrix<double> D(2, 3);
+  for (int i = 0; i < 6; ++i) D.value()[i] = i + 1;         // [1 2 3; 4 5 6]
+  const Matrix<double>& Dm = D;  // the SArray overloads live in the base class
+  EXPECT((Dm.times(SArray<double>({1, 0, 1})) == SArray<double>({4, 10})));
+  EXPECT((Dm.transTimes(SArray<double>({1, 1})) == SArray<double>({5, 7, 9})));
+}
+
+void checkLocalizer(Checks& ck) {
+  SArray<uint64> idx = {50, 7, 7, 900, 50, 7, 3};
+  SArray<uint64> uniq;
+  SArray<uint8> cnt;
+  Localizer<uint64, double> lc;
+  lc.countUniqIndex(idx, &uniq, &cnt);
+  EXPECT((uniq == SArray<uint64>({3, 7, 50, 900})) && (cnt == SArray<uint8>({1, 3, 2, 1})));
+  // 300 copies of one key saturate an 8-bit count instead of wrapping to 44
+  SArray<uint64> many(300);
+  many.setValue(5);
+  SArray<uint64> u2;
+  SArray<uint8> c2;
+  Localizer<uint64, double> l2;
+  l2.countUniqIndex(many, &u2, &c2);
+  EXPECT(u2.size() == 1 && c2[0] == 255);
+  // remap rows {50 7 | 7 900 50 | 7 3} onto the dictionary {7, 50}: columns 0/1, others dropped
+  MatrixInfo info;
+  info.set_type(MatrixInfoView::SPARSE);
+  info.set_row_major(true);
+  info.mutable_row().set_begin(0); info.mutable_row().set_end(3);
+  info.mutable_col().set_begin(0); info.mutable_col().set_end(1000);
+  info.set_nnz(7);
+  SArray<size_t> off = {0, 2, 5, 7};
+  SArray<double> val = {1, 2, 3, 4, 5, 6, 7};
+  MatrixPtr<double> X = lc.remapIndex(info, off, idx, val, SArray<uint64>({7, 50}));
+  EXPECT(X && X->rows() == 3 && X->cols() == 2 && X->nnz() == 5);
+  EXPECT((X->times(SArray<double>({1, 10})) == SArray<double>({12, 53, 6})));
+}
+
+void checkMatch(Checks& ck) {
+  SArray<uint64> sk = {2, 4, 6, 8};
+  SArray<double> sv = {20, 40, 60, 80};
+  SArray<uint64> dk = {1, 2, 3, 6, 7, 8, 9};
+  SArray<double> dv;
+  size_t n = parallelOrderedMatch<uint64, double>(sk, sv, dk, &dv);
+  EXPECT(n == 3 && (dv == SArray<double>({0, 20, 0, 60, 0, 80, 0})));
+  n = parallelOrderedMatch<uint64, double, OpPlus<double>>(sk, sv, dk, &dv);
+  EXPECT(n == 3 && dv[1] == 40 && dv[5] == 160);
+  SArray<uint64> ko;
+  SArray<double> vo;
+  parallelUnion<uint64, double>(sk, sv, SArray<uint64>({4, 5}), SArray<double>({1, 2}), &ko, &vo);
+  EXPECT((ko == SArray<uint64>({2, 4, 5, 6, 8})) && (vo == SArray<double>({20, 41, 2, 60, 80})));
+  SArray<int> big(200000);
+  uint32 s = 12345;
+  for (size_t i = 0; i < big.size(); ++i) { s = s * 1664525u + 1013904223u; big[i] = (int)(s >> 8); }
+  parallelSort(&big, 4, [](int a, int b) { return a < b; });
+  EXPECT(std::is_sorted(big.begin(), big.end()));
+}
+
+void checkConcurrent(Checks& ck) {
+  std::atomic<int> sum(0);
+  {
+    ThreadPool pool(4);
+    for (int i = 1; i <= 100; ++i) pool.add([&sum, i] { sum += i; });
+    pool.startWorkers();
+  }
+  EXPECT(sum == 5050);
+  threadsafe_queue<int> q;
+  std::thread prod([&] { for (int i = 0; i < 1000; ++i) q.push(i); });
+  long got = 0;
+  for (int i = 0; i < 1000; ++i) { int v; q.wait_and_pop(v); got += v; }
+  prod.join();
+  EXPECT(got == 499500);
+  Barrier bar(3);
+  std::atomic<int> leaders(0);
+  std::vector<std::thread> th;
+  for (int i = 0; i < 3; ++i) th.emplace_back([&] { if (bar.block()) ++leaders; });
+  for (auto& t : th) t.join();
+  EXPECT(leaders == 1);
+  Range<uint64> r(10, 110);
+  EXPECT(r.evenDivide(4, 3).end() == 110 && r.evenDivide(4, 0).begin() == 10 && r.size() == 100);
+  EXPECT(r.setIntersection(Range<uint64>(100, 500)) == Range<uint64>(100, 110));
+  Timer t;
+  t.start();
+  std::this_thread::sleep_for(std::chrono::milliseconds(20));
+  EXPECT(t.stop() >= 0.015);
+}
+#undef EXPECT
+}  // namespace
+
+PSH_API int psh_selftest(const char* area, int32_t* n_checks) {
+  string a = area ? area : "all";
+  Checks ck;
+  if (a == "all" || a == "bitmap") checkBitmap(ck);
+  if (a == "all" || a == "sarray") checkSArray(ck);
+  if (a == "all" || a == "matrix") checkMatrix(ck);
+  if (a == "all" || a == "localizer") checkLocalizer(ck);
+  if (a == "all" || a == "match") checkMatch(ck);
+  if (a == "all" || a == "concurrent") checkConcurrent(ck);
+  if (n_checks) *n_checks = ck.n;
+  if (ck.n == 0) return fail("unknown self-test area '" + a + "'");
+  if (!ck.err.str().empty()) return fail("check failed: " + ck.err.str());
+  return 0;
+}
+
 // ---- diagnostics ---------------------------------------------------------------------------------------
 #include <execinfo.h>
 #include <signal.h>

@@ -253,3 +253,11 @@ def run_reassign_scenario(num_servers: int, num_workers: int, lo: int, hi: int) 
         i, b, e = line.split()
         out[i] = (int(b), int(e))
     return out
+
+
+def selftest(area: str = "all") -> int:
+    """Run the native unit checks of one area (bitmap, sarray, matrix, localizer, match,
+    concurrent) or all of them; returns the number of checks, raises on the first failure."""
+    n = C.c_int32(0)
+    hcheck(_lib().psh_selftest(area.encode(), C.byref(n)))
+    return int(n.value)

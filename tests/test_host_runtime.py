@@ -177,3 +177,12 @@ def test_reassign_server_key_range():
         r = Range(0, 100).even_divide(3, s)
         assert got[f"S{s}"] == (r.begin, r.end)
     assert all(got[f"W{w}"] == (0, 100) for w in range(3))
+
+
+@pytest.mark.parametrize("area", ["bitmap", "sarray", "matrix", "localizer", "match", "concurrent"])
+def test_native_util_checks(area):
+    """C++-side checks in capi.cc mirroring the reference's bitmap / shared_array / sparse_matrix /
+    localizer / common unit tests"""
+    assert host.selftest(area) >= 3
+    with pytest.raises(Exception):
+        host.selftest("no-such-area")
