@@ -23,4 +23,11 @@ sass: all
 clean:
 	rm -rf build parameter_server_b200/lib
 
-.PHONY: all force test test-gpu bench sass clean
+.PHONY: all force test test-gpu bench sass clean tsan asan
+
+# host runtime under sanitizers (build/selftest: native unit checks + in-process clusters + apps)
+tsan:
+	$(PY) tools/sanitize.py thread
+
+asan:
+	$(PY) tools/sanitize.py address

@@ -9,7 +9,7 @@ namespace PS {
 namespace LM {
 
 App* createApp(const string& name, const ConfigView& conf) {
-  NodeView my_node = Postoffice::current().myNode();
+  Node my_node = Postoffice::current().myNode();
   auto role = my_node.role();
   App* app = nullptr;
   if (conf.has_darlin()) {

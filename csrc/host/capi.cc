@@ -403,7 +403,7 @@ PSH_API int psh_run_kv_cluster(int32_t num_servers, int32_t num_workers, int32_t
   std::vector<float> got;
   std::mutex mu;
   auto factory = [&](const string& name, const string&) -> App* {
-    NodeView me = Postoffice::current().myNode();
+    Node me = Postoffice::current().myNode();
     if (me.role() == NodeView::SERVER) return new KVServerApp(name, n_keys);
     if (me.role() == NodeView::WORKER) return new KVWorkerApp(name, keys, &got, &mu);
     return new App(name);
@@ -582,7 +582,7 @@ PSH_API int psh_run_replace_scenario(int32_t n_keys, float* out_vals, uint64_t* 
   c.add(NodeView::WORKER, "W0");
   c.add(NodeView::UNUSED, "U0");
   auto factory = [&](const string& name, const string&) -> App* {
-    NodeView me = Postoffice::current().myNode();
+    Node me = Postoffice::current().myNode();
     if (me.role() == NodeView::SERVER) return new ReplServerApp(name, n_keys);
     if (me.role() == NodeView::WORKER) return new ReplWorkerApp(name, n_keys, &got, &gate);
     return new App(name);
@@ -629,7 +629,7 @@ PSH_API int psh_run_heartbeat_scenario(int32_t interval_s, int32_t run_ms, int32
   c.add(NodeView::WORKER, "W0");
   c.add(NodeView::WORKER, "W1");
   auto factory = [&](const string& name, const string&) -> App* {
-    NodeView me = Postoffice::current().myNode();
+    Node me = Postoffice::current().myNode();
     if (me.role() == NodeView::WORKER) return new SleepWorkerApp(name, run_ms);
     return new App(name);
   };
@@ -751,7 +751,7 @@ PSH_API int psh_run_reassign_scenario(int32_t num_servers, int32_t num_workers, 
   for (int i = 0; i < num_servers; ++i) c.add(NodeView::SERVER, "S" + to_string(i));
   for (int i = 0; i < num_workers; ++i) c.add(NodeView::WORKER, "W" + to_string(i));
   auto factory = [&](const string& name, const string&) -> App* {
-    NodeView me = Postoffice::current().myNode();
+    Node me = Postoffice::current().myNode();
     if (me.role() == NodeView::SCHEDULER) return new ReassignRoot(name, lo, hi);
     return new ReassignSlave(name, &got, &mu);
   };

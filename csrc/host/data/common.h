@@ -76,6 +76,9 @@ inline DataConfig searchFiles(const DataConfigView& config) {
     const string base = getFilename(config.file(i));
     std::regex pattern;
     try {
+      // libstdc++ fills a per-locale narrow() cache while compiling: one compilation at a time
+      static std::mutex regex_mu;
+      Lock l(regex_mu);
       pattern = std::regex(base);
     } catch (const std::regex_error& e) {
       CHECK(false) << base << " is not a valid regex: " << e.what();

@@ -751,12 +751,14 @@ void Postoffice::start(int* argc, char*** argv) {
 
 void Postoffice::start(const PostofficeOptions& opt) {
   opt_ = opt;
+  my_id_ = opt_.my_node.id();
+  my_role_ = (int)opt_.my_node.role();
   setCurrent(this);
-  const bool scheduler = opt_.my_node.role() == NodeView::SCHEDULER;
+  const bool scheduler = my_role_ == (int)NodeView::SCHEDULER;
   if (opt_.fabric) yp_.setVan(unique_ptr<Van>(new InprocVan(opt_.fabric)));
   else yp_.setVan(unique_ptr<Van>(new TcpVan()));
   CHECK(yp_.van().init(opt_.my_node)) << "van init failed for " << opt_.my_node.ShortDebugString();
-  if (opt_.print_van) yp_.van().enableLog("van_" + opt_.my_node.id());
+  if (opt_.print_van) yp_.van().enableLog("van_" + my_id_);
   yp_.addNode(opt_.my_node);
   if (!scheduler) yp_.addNode(opt_.scheduler);
   hb_info_->init(opt_.my_node.hostname());
@@ -781,9 +783,9 @@ void Postoffice::start(const PostofficeOptions& opt) {
     task.set_time(0);
     task.set_customer(opt_.app_name);
     task.mutable_mng_node().set_cmd(ManageNodeView::CONNECT);
-    task.mutable_mng_node().add_node().raw()->copyFrom(*opt_.my_node.raw());
+    task.mutable_mng_node().add_node().raw()->copyFrom(*myNode().raw());
     MessagePtr msg(new Message(task));
-    msg->sender = opt_.my_node.id();
+    msg->sender = my_id_;
     msg->recver = opt_.scheduler.id();
     queue(msg);
 
@@ -810,7 +812,7 @@ void Postoffice::start(const PostofficeOptions& opt) {
     Task add;
     add.set_customer(app_->name());
     add.mutable_mng_node().set_cmd(ManageNodeView::ADD);
-    add.mutable_mng_node().add_node().raw()->copyFrom(*opt_.my_node.raw());
+    add.mutable_mng_node().add_node().raw()->copyFrom(*myNode().raw());
     manageNode(add);
   }
   if (opt_.num_workers + opt_.num_servers == 0) {
@@ -870,7 +872,7 @@ void Postoffice::finishBarrier(int which) {
 }
 
 void Postoffice::stop() {
-  const bool scheduler = opt_.my_node.role() == NodeView::SCHEDULER;
+  const bool scheduler = my_role_ == (int)NodeView::SCHEDULER;
   if (scheduler) {
     if (opt_.num_workers + opt_.num_servers) {
       std::unique_lock<std::mutex> l(mu_);
@@ -902,7 +904,7 @@ void Postoffice::reply(const NodeID& recver, const TaskView& task, const string&
   if (!reply_msg.empty()) tk.set_msg(reply_msg);
   tk.set_time(task.time());
   MessagePtr re(new Message(tk));
-  re->sender = opt_.my_node.id();
+  re->sender = my_id_;
   re->recver = recver;
   queue(re);
 }
@@ -952,7 +954,7 @@ void Postoffice::recv() {
     if (type == TaskView::CALL_CUSTOMER || type == TaskView::REPLY) {
       Customer* c = yp_.customer(tk.customer());
       if (!c) {
-        LL << opt_.my_node.id() << ": customer [" << tk.customer() << "] does not exist, dropped "
+        LL << my_id_ << ": customer [" << tk.customer() << "] does not exist, dropped "
            << msg->shortDebugString();
         continue;
       }
@@ -1032,7 +1034,7 @@ void Postoffice::manageNode(const TaskView& tk) {
   ManageNodeView mng = tk.mng_node();
   switch (mng.cmd()) {
     case ManageNodeView::CONNECT: {
-      CHECK(opt_.my_node.role() == NodeView::SCHEDULER);
+      CHECK(my_role_ == (int)NodeView::SCHEDULER);
       CHECK_EQ(mng.node_size(), 1);
       NodeView node = mng.node(0);
       if (node.role() == NodeView::UNUSED) {  // hot spare: remember it, do not start an app yet
@@ -1070,7 +1072,11 @@ void Postoffice::manageNode(const TaskView& tk) {
       for (int i = 0; i < mng.node_size(); ++i) {
         NodeView node = mng.node(i);
         yp_.addNode(node);
-        if (node.id() == opt_.my_node.id()) opt_.my_node = node;
+        if (node.id() == my_id_) {
+          Lock l(my_node_mu_);
+          opt_.my_node = node;
+          my_role_ = (int)node.role();
+        }
         obj->exec().add(node);
         for (const auto& c : yp_.childern(obj->name())) {
           Customer* child = yp_.customer(c);
@@ -1084,7 +1090,11 @@ void Postoffice::manageNode(const TaskView& tk) {
       yp_.removeNode(mng.node(0).id());
       yp_.addNode(mng.node(1));
       // a spare learns its new role here, before its app exists (the factory looks at the role)
-      if (mng.node(1).id() == opt_.my_node.id()) opt_.my_node = mng.node(1);
+      if (mng.node(1).id() == my_id_) {
+        Lock l(my_node_mu_);
+        opt_.my_node = mng.node(1);
+        my_role_ = (int)mng.node(1).role();
+      }
       Customer* obj = yp_.customerIfPresent(tk.customer());
       if (!obj) break;
       obj->exec().replace(mng.node(0), mng.node(1));
@@ -1111,7 +1121,7 @@ void Postoffice::manageNode(const TaskView& tk) {
 }
 
 void Postoffice::replaceNode(const NodeView& dead, const NodeView& live) {
-  CHECK(opt_.my_node.role() == NodeView::SCHEDULER);
+  CHECK(my_role_ == (int)NodeView::SCHEDULER);
   Node nw(live);
   nw.set_role(dead.role());
   nw.set_rank(dead.rank());
@@ -1179,7 +1189,7 @@ std::vector<string> Postoffice::deadNodes(int timeout_sec) { return dashboard_->
 // periodic heartbeat: every node reports resource usage to the scheduler, which keeps the
 // dashboard and (with -enable_fault_tolerance) swaps overdue nodes for unused ones
 void Postoffice::heartbeat() {
-  const bool scheduler = opt_.my_node.role() == NodeView::SCHEDULER;
+  const bool scheduler = my_role_ == (int)NodeView::SCHEDULER;
   int tick = 0;
   while (!done_) {
     for (int i = 0; i < opt_.report_interval * 10 && !done_; ++i)
@@ -1187,7 +1197,7 @@ void Postoffice::heartbeat() {
     if (done_) break;
     HeartbeatReport rep = hb_info_->get();
     if (scheduler) {
-      dashboard_->addReport(opt_.my_node.id(), rep);
+      dashboard_->addReport(my_id_, rep);
       if (++tick % 5 == 0 && FLAGS_verbose) fprintf(stderr, "%s\n", dashboard_->report().c_str());
       if (FLAGS_enable_fault_tolerance) {
         for (const string& id : dashboard_->deadNodes(opt_.report_interval * 5)) {
@@ -1211,7 +1221,7 @@ void Postoffice::heartbeat() {
       tk.set_request(false);
       tk.set_msg(rep.SerializeAsString());
       MessagePtr m(new Message(tk));
-      m->sender = opt_.my_node.id();
+      m->sender = my_id_;
       m->recver = opt_.scheduler.id();
       queue(m);
     }

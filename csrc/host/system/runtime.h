@@ -140,8 +140,10 @@ class Executor {
   RNodePtr rnode(const NodeID& k);
   std::vector<RNodePtr> group(const NodeID& k);
   KeyRangeList keyRanges(const NodeID& k);
-  const Node& myNode() const { return my_node_; }
-  void setMyNode(const NodeView& n) { my_node_ = n; }
+  // a copy taken under the lock: rank and key range of this node change when the scheduler
+  // assigns them (ManageNode ADD / UPDATE / REPLACE) while app threads are reading
+  Node myNode() const { Lock l(node_mu_); return my_node_; }
+  void setMyNode(const NodeView& n) { Lock l(node_mu_); my_node_ = n; }
   Customer& obj() { return obj_; }
   Postoffice& sys() { return sys_; }
 
@@ -166,7 +168,7 @@ class Executor {
   Customer& obj_;
   Postoffice& sys_;
   Node my_node_;
-  std::mutex node_mu_;
+  mutable std::mutex node_mu_;
   std::map<NodeID, NodeInfo> nodes_;
   std::mutex recved_msg_mu_;
   std::condition_variable dag_cond_;
@@ -194,7 +196,7 @@ class Customer {
   Postoffice& sys() { return sys_; }
   RNodePtr port(const NodeID& k) { return exec_->rnode(k); }
 
-  const Node& myNode() { return exec_->myNode(); }
+  Node myNode() { return exec_->myNode(); }
   NodeID myNodeID() { return exec_->myNode().id(); }
   int myRank() { return exec_->myNode().rank(); }
   bool isWorker() { return exec_->myNode().role() == NodeView::WORKER; }
@@ -315,7 +317,8 @@ class Postoffice {
   }
 
   YellowPages& yp() { return yp_; }
-  Node& myNode() { return opt_.my_node; }
+  Node myNode() { Lock l(my_node_mu_); return opt_.my_node; }
+  const string& myID() const { return my_id_; }  // never changes after start()
   Node& scheduler() { return opt_.scheduler; }
   const PostofficeOptions& options() const { return opt_; }
   App* app() { return app_.get(); }
@@ -340,6 +343,9 @@ class Postoffice {
   void finishBarrier(int n);
 
   PostofficeOptions opt_;
+  std::mutex my_node_mu_;            // guards opt_.my_node after start()
+  string my_id_;                     // = opt_.my_node.id(), immutable
+  std::atomic<int> my_role_{0};      // changes once at most (a spare taking over a role)
   YellowPages yp_;
   unique_ptr<App> app_;
   threadsafe_queue<MessagePtr> sending_queue_;

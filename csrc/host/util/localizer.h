@@ -124,7 +124,8 @@ class Localizer {
     for (size_t i = 0; i < n; ++i) {
       ++run;
       if (i + 1 == n || pair_[i + 1].k != pair_[i].k) {
-        uniq_idx->pushBack(pair_[i].k);
+        const I key = pair_[i].k;  // the pairs are packed: never bind a reference to the field
+        uniq_idx->pushBack(key);
         if (idx_frq) idx_frq->pushBack((C)std::min<uint64>(run, cmax));
         run = 0;
       }

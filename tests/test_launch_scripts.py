@@ -84,3 +84,13 @@ def test_text2proto_and_show_example(tmp_path):
     assert g.n_rows == 200 and g.nnz == shard.nnz
     import torch
     assert torch.equal(g.keys, shard.keys)
+
+
+def test_selftest_binary():
+    """build/selftest: native unit checks, in-process clusters, node replacement, apps. The same
+    binary is what tools/sanitize.py runs under ThreadSanitizer / AddressSanitizer (make tsan / asan)."""
+    exe = ROOT / "build" / "selftest"
+    assert exe.exists()
+    r = subprocess.run([str(exe), "all"], capture_output=True, text=True, timeout=170)
+    assert r.returncode == 0 and "0 failure(s)" in r.stderr, r.stderr[-3000:]
+    assert r.stderr.count("\nok ") + r.stderr.startswith("ok ") >= 11
