@@ -3,7 +3,7 @@
     python tools/sanitize.py thread      # ThreadSanitizer
     python tools/sanitize.py address     # AddressSanitizer + UBSan
 
-Objects go to build/san-<kind>/ (the normal build is untouched). Exit code = the binary's.
+Objects go to $TMPDIR/psb200-san-<kind>/ (the normal build is untouched). Exit code = the binary's.
 """
 import os
 import subprocess
@@ -18,7 +18,8 @@ HOST = ROOT / "csrc" / "host"
 def main() -> int:
     kind = sys.argv[1] if len(sys.argv) > 1 else "thread"
     flags = {"thread": ["-fsanitize=thread"], "address": ["-fsanitize=address,undefined", "-fno-omit-frame-pointer"]}[kind]
-    out = ROOT / "build" / f"san-{kind}"
+    # outside the tree: these objects are large and must not travel with repository snapshots
+    out = Path(os.environ.get("TMPDIR", "/tmp")) / f"psb200-san-{kind}"
     out.mkdir(parents=True, exist_ok=True)
     # the sanitizer runtimes ship with the distribution compiler, not with every custom toolchain
     cxx = os.environ.get("SAN_CXX") or ("/usr/bin/g++" if os.path.exists("/usr/bin/g++") else os.environ.get("CXX", "g++"))
