@@ -235,14 +235,9 @@ __device__ __forceinline__ float prox_enet(float z, float eta, float l1, float l
   return z > 0 ? (z - leta) / (1.f + l2 * eta) : (z + leta) / (1.f + l2 * eta);
 }
 
-// one launch per worker (rounds must not interleave: two workers may push the same key)
-__global__ void __launch_bounds__(kSgdThreads)
-k_sgd_server(const __grid_constant__ SgdServer S, int wkr, uint64_t seq) {
-  __shared__ double sh[3][kSgdWarps];
-  const int64_t gt = (int64_t)blockIdx.x * kSgdThreads + threadIdx.x, nt = (int64_t)gridDim.x * kSgdThreads;
-  double d_nnz = 0, d_w2 = 0, d_d2 = 0;
-  if (threadIdx.x == 0) spin_or_fault(S.land_flag + wkr, seq, 2, S.rank * 100 + wkr);
-  __syncthreads();
+// apply push `seq` of worker `wkr` to the shard (threads gt, gt + nt, ...); returns the statistics deltas
+__device__ __forceinline__ void sgd_apply_worker(const SgdServer& S, int wkr, uint64_t seq, int64_t gt, int64_t nt,
+                                                 double& d_nnz, double& d_w2, double& d_d2) {
   const int64_t region = (int64_t)(seq % (uint64_t)S.depth);
   const int64_t n = __ldcg(S.land_cnt + (int64_t)wkr * S.depth + region);
   const int64_t base = ((int64_t)wkr * S.depth + region) * S.land_cap;
@@ -278,6 +273,10 @@ k_sgd_server(const __grid_constant__ SgdServer S, int wkr, uint64_t seq) {
     d_w2 += (double)w_new * w_new;
     d_d2 += (double)(w_new - w_old) * (w_new - w_old);
   }
+}
+
+__device__ __forceinline__ void sgd_flush_stats(const SgdServer& S, double d_nnz, double d_w2, double d_d2,
+                                                double (*sh)[kSgdWarps]) {
   d_nnz = warp_sum(d_nnz); d_w2 = warp_sum(d_w2); d_d2 = warp_sum(d_d2);
   const int wid = threadIdx.x >> 5;
   if ((threadIdx.x & 31) == 0) { sh[0][wid] = d_nnz; sh[1][wid] = d_w2; sh[2][wid] = d_d2; }
@@ -289,6 +288,44 @@ k_sgd_server(const __grid_constant__ SgdServer S, int wkr, uint64_t seq) {
     if (b != 0) atomicAdd(S.stats + 1, b);
     if (c != 0) atomicAdd(S.stats + 2, c);
   }
+}
+
+// one launch per worker (rounds must not interleave: two workers may push the same key)
+__global__ void __launch_bounds__(kSgdThreads)
+k_sgd_server(const __grid_constant__ SgdServer S, int wkr, uint64_t seq) {
+  __shared__ double sh[3][kSgdWarps];
+  const int64_t gt = (int64_t)blockIdx.x * kSgdThreads + threadIdx.x, nt = (int64_t)gridDim.x * kSgdThreads;
+  double d_nnz = 0, d_w2 = 0, d_d2 = 0;
+  if (threadIdx.x == 0) spin_or_fault(S.land_flag + wkr, seq, 2, S.rank * 100 + wkr);
+  __syncthreads();
+  sgd_apply_worker(S, wkr, seq, gt, nt, d_nnz, d_w2, d_d2);
+  sgd_flush_stats(S, d_nnz, d_w2, d_d2, sh);
+}
+
+// The same in ONE cooperative launch: workers in rank order, a grid barrier between two workers
+// (their pushes may contain the same key), acknowledgements at the end.  2 launches per minibatch
+// step instead of 2 + n_workers.
+__global__ void __launch_bounds__(kSgdThreads)
+k_sgd_server_all(const __grid_constant__ SgdServer S, uint64_t seq, uint32_t* bar) {
+  __shared__ double sh[3][kSgdWarps];
+  const int64_t gt = (int64_t)blockIdx.x * kSgdThreads + threadIdx.x, nt = (int64_t)gridDim.x * kSgdThreads;
+  const uint32_t G = gridDim.x;
+  double d_nnz = 0, d_w2 = 0, d_d2 = 0;
+  for (int wkr = 0; wkr < S.n_workers; ++wkr) {
+    if (threadIdx.x == 0) spin_or_fault(S.land_flag + wkr, seq, 2, S.rank * 100 + wkr);
+    __syncthreads();
+    sgd_apply_worker(S, wkr, seq, gt, nt, d_nnz, d_w2, d_d2);
+    grid_arrive(bar);
+    if (wkr + 1 < S.n_workers) grid_wait(bar, (uint32_t)(wkr + 1) * G);
+  }
+  sgd_flush_stats(S, d_nnz, d_w2, d_d2, sh);
+  if (blockIdx.x != 0) return;  // everybody has arrived at the last barrier; only block 0 waits
+  grid_wait(bar, (uint32_t)S.n_workers * G);
+  if (threadIdx.x < S.n_workers) {
+    __threadfence_system();
+    st_release_sys(S.ack_out[threadIdx.x], seq);
+  }
+  if (threadIdx.x == 0) *bar = 0;
 }
 
 // tell every worker that its push `seq` has been applied: its ring slot may be reused
@@ -394,6 +431,23 @@ PSB_API int psb_sgd_server_update(const psb_sgd_server* sv, uint64_t seq, int32_
   }
   k_sgd_ack<<<1, 32, 0, (cudaStream_t)stream>>>(*sv, seq);
   PSB_LAUNCH_CHECK();
+  return 0;
+}
+
+// The same as psb_sgd_server_update in one cooperative launch (k_sgd_server_all).  `bar`: one zeroed
+// uint32 owned by the caller; `grid` is clamped to what is co-resident.
+PSB_API int psb_sgd_server_update_fused(const psb_sgd_server* sv, uint64_t seq, int32_t grid, uint32_t* bar,
+                                        void* stream) {
+  PSB_REQUIRE(sv && bar && grid >= 1, "psb_sgd_server_update_fused: bad argument");
+  PSB_REQUIRE(sv->n_workers >= 1 && sv->n_workers <= PSB_MAX_PEERS && sv->depth >= 1,
+              "psb_sgd_server_update_fused: bad struct");
+  int per_sm = 0;
+  PSB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_sgd_server_all, kSgdThreads, 0));
+  PSB_REQUIRE(per_sm >= 1, "psb_sgd_server_update_fused: kernel does not fit on an SM");
+  grid = min(grid, per_sm * sm_count());
+  void* args[] = {(void*)sv, (void*)&seq, (void*)&bar};
+  PSB_CUDA(cudaLaunchCooperativeKernel((const void*)k_sgd_server_all, dim3(grid), dim3(kSgdThreads), args, 0,
+                                       (cudaStream_t)stream));
   return 0;
 }
 

@@ -607,6 +607,9 @@ PSH_API int psh_run_replace_scenario(int32_t n_keys, float* out_vals, uint64_t* 
       if (r.contains(spreadKey(i, n_keys))) { lo = std::min(lo, i); hi = std::max(hi, i + 1); }
     s1_range2[0] = lo; s1_range2[1] = hi;
   }
+  // replication is asynchronous (a push is acknowledged before its copy reaches the replica
+  // holder): give the forwarded pushes time to land before the crash
+  std::this_thread::sleep_for(std::chrono::milliseconds(300));
   c.offices[c.index("S1")]->kill();
   sched.replaceNode(dead, live);
   gate.set(2);

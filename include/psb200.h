@@ -275,6 +275,10 @@ int psb_sgd_worker_step(const psb_sgd_worker* wk, uint64_t seq, int32_t grid, ui
 /* K8: wait (on the device) for push `seq` of every worker, apply them in worker order, then
  * acknowledge to the workers. */
 int psb_sgd_server_update(const psb_sgd_server* sv, uint64_t seq, int32_t grid, void* stream);
+/* The same in ONE cooperative launch (workers in rank order behind grid barriers, then the
+ * acknowledgements): 2 launches per minibatch step instead of 2 + n_workers.  bar: zeroed uint32. */
+int psb_sgd_server_update_fused(const psb_sgd_server* sv, uint64_t seq, int32_t grid, uint32_t* bar,
+                                void* stream);
 
 
 /* ------------------------------------------------------------------------- *

@@ -72,6 +72,7 @@ class AsyncSGDConfig:
     fixing_float_by_nbytes: int = 0  # != 0 -> int8 block-scaled push (K9)
     table_capacity: int = 1 << 22    # slots per shard (power of two)
     report_every: int = 10           # minibatches between progress lines
+    fused_server: bool = True        # one cooperative server launch per step instead of 1 + n_workers
 
     @staticmethod
     def from_proto_text(conf_text: str) -> "AsyncSGDConfig":
@@ -119,6 +120,7 @@ def _lib():
         lib.psb_kv_export_nonzero.argtypes = [P, P, C.c_int64, P, P, P, P]
         lib.psb_sgd_worker_step.argtypes = [P, C.c_uint64, C.c_int32, P, P]
         lib.psb_sgd_server_update.argtypes = [P, C.c_uint64, C.c_int32, P]
+        lib.psb_sgd_server_update_fused.argtypes = [P, C.c_uint64, C.c_int32, P, P]
         lib.psb_sgd_max_grid.restype = C.c_int
         lib.psb_sgd_set_fault_sink.argtypes = [P]
         lib._sgd_sigs = True
@@ -179,6 +181,7 @@ class AsyncSGDEngine:
         self.wstats = torch.zeros(4, **f64)
         self.sstats = torch.zeros(4, **f64)
         self.bar = torch.zeros(4, dtype=torch.int32, device=dev)
+        self.srv_bar = torch.zeros(4, dtype=torch.int32, device=dev)
         self.overflow = torch.zeros(1, dtype=torch.int32, device=dev)
         self.grid = int(self.lib.psb_sgd_max_grid())
         # device waits that time out report here instead of hanging the GPU (sgd.cu spin_or_fault)
@@ -306,9 +309,14 @@ class AsyncSGDEngine:
     def server_step(self) -> None:
         """Server half: apply push `seq` of every worker in rank order, acknowledge."""
         self.sv.sgd_t = math.sqrt(self.seq)
-        check(self.lib.psb_sgd_server_update(C.byref(self.sv), self.seq, self.grid_server,
-                                             current_stream()))
-        self.launches += 1 + self.world
+        if self.cfg.fused_server:
+            check(self.lib.psb_sgd_server_update_fused(C.byref(self.sv), self.seq, self.grid_server,
+                                                       self.srv_bar.data_ptr(), current_stream()))
+            self.launches += 1
+        else:
+            check(self.lib.psb_sgd_server_update(C.byref(self.sv), self.seq, self.grid_server,
+                                                 current_stream()))
+            self.launches += 1 + self.world
 
     def check_table_load(self) -> float:
         """Open addressing with linear probing degrades sharply when a shard's table fills up
