@@ -105,22 +105,7 @@ def main(argv=None) -> int:
         groups = load_slot_data(data_conf_for(conf, "training_data", mine), cache)
         if has("darlin"):
             from ..models.darlin import DarlinConfig, DarlinEngine
-            g = lambda k, d: host.textproto_get(conf, "linear_method." + k) or d  # noqa: E731
-            cfg = DarlinConfig(
-                lambda_l1=float(g("penalty.lambda[0]", 1)), eta=float(g("learning_rate.alpha", 1)),
-                max_pass_of_data=int(g("darlin.max_pass_of_data", 10)), epsilon=float(g("darlin.epsilon", 1e-4)),
-                feature_block_ratio=float(g("darlin.feature_block_ratio", 4)),
-                random_feature_block_order=g("darlin.random_feature_block_order", "true") == "true",
-                max_block_delay=int(g("darlin.max_block_delay", 0)),
-                tail_feature_freq=int(g("darlin.tail_feature_freq", 0)),
-                num_iter_for_prior_fea_group=int(g("darlin.num_iter_for_prior_fea_group", 5)),
-                delta_init_value=float(g("darlin.[PS.LM.delta_init_value]", 1)),
-                delta_max_value=float(g("darlin.[PS.LM.delta_max_value]", 5)),
-                kkt_filter_threshold_ratio=float(g("darlin.[PS.LM.kkt_filter_threshold_ratio]", 10)))
-            i = 0
-            while host.textproto_get(conf, f"linear_method.darlin.prior_fea_group[{i}]"):
-                cfg.prior_fea_group.append(int(host.textproto_get(conf, f"linear_method.darlin.prior_fea_group[{i}]")))
-                i += 1
+            cfg = DarlinConfig.from_proto_text(conf)
             eng = DarlinEngine(cfg, comm, dev)
             eng.load(groups)
             eng.train()

@@ -67,30 +67,33 @@ class DarlinConfig:
     profile_phases: bool = False      # accumulate per-phase %globaltimer time (debug)
 
     @staticmethod
-    def from_proto(conf) -> "DarlinConfig":
-        """Build from a parsed LM config (utils.config.Message)."""
-        d = conf.get("darlin")
+    def from_proto_text(conf_text: str) -> "DarlinConfig":
+        """From the text of an AppConfig (`linear_method { ... darlin { ... } }`, linear.proto /
+        bcd.proto incl. the `[PS.LM.*]` extensions); fields that are absent keep the proto defaults."""
+        from ..runtime.host import textproto_get
+        base = "linear_method."
+        g = lambda k: textproto_get(conf_text, base + k)  # noqa: E731
         c = DarlinConfig()
-        pen = conf.get("penalty")
-        if pen is not None and pen.get_all("lambda"):
-            c.lambda_l1 = float(pen.get_all("lambda")[0])
-        lr = conf.get("learning_rate")
-        if lr is not None and lr.get("alpha") is not None:
-            c.eta = float(lr.get("alpha"))
-        if d is not None:
-            for name in ("max_pass_of_data", "epsilon", "feature_block_ratio",
-                         "random_feature_block_order", "max_block_delay", "tail_feature_freq",
-                         "num_iter_for_prior_fea_group", "countmin_k", "countmin_n_ratio"):
-                v = d.get(name)
-                if v is not None:
-                    setattr(c, name, type(getattr(c, name))(v))
-            c.prior_fea_group = [int(x) for x in d.get_all("prior_fea_group")]
-            for ext, name in (("PS.LM.delta_init_value", "delta_init_value"),
-                              ("PS.LM.delta_max_value", "delta_max_value"),
-                              ("PS.LM.kkt_filter_threshold_ratio", "kkt_filter_threshold_ratio")):
-                v = d.get("[" + ext + "]")
-                if v is not None:
-                    setattr(c, name, float(v))
+        if g("penalty.lambda[0]"):
+            c.lambda_l1 = float(g("penalty.lambda[0]"))
+        if g("learning_rate.alpha"):
+            c.eta = float(g("learning_rate.alpha"))
+        for name in ("max_pass_of_data", "epsilon", "feature_block_ratio", "max_block_delay", "tail_feature_freq",
+                     "num_iter_for_prior_fea_group", "countmin_k", "countmin_n_ratio"):
+            v = g("darlin." + name)
+            if v:
+                setattr(c, name, type(getattr(c, name))(float(v)))
+        v = g("darlin.random_feature_block_order")
+        if v:
+            c.random_feature_block_order = v == "true"
+        for ext in ("delta_init_value", "delta_max_value", "kkt_filter_threshold_ratio"):
+            v = g(f"darlin.[PS.LM.{ext}]")
+            if v:
+                setattr(c, ext, float(v))
+        i = 0
+        while g(f"darlin.prior_fea_group[{i}]"):
+            c.prior_fea_group.append(int(g(f"darlin.prior_fea_group[{i}]")))
+            i += 1
         return c
 
 
