@@ -1,7 +1,7 @@
 // build/selftest: the native unit checks and the in-process cluster scenarios in one binary, so
 // that they can run under ThreadSanitizer / AddressSanitizer (tools/sanitize.py) - the reference has
 // no sanitizer story at all.
-//   build/selftest [all|units|kv|ring|replace|heartbeat|reassign|apps]
+//   build/selftest [all|units|kv|kvmap|ring|replace|heartbeat|reassign|apps]
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -20,6 +20,7 @@ int psh_run_heartbeat_scenario(int32_t interval_s, int32_t run_ms, int32_t dead_
                                int64_t cap, int64_t* len, int32_t* n_dead);
 int psh_run_cluster(const char* app_conf_text, int32_t num_servers, int32_t num_workers, int32_t use_tcp,
                     int32_t base_port, int32_t message_compression, char* report_out, int64_t cap, int64_t* len);
+int psh_run_kvmap_scenario(int32_t n_keys, double* out_vals);
 int psh_run_reassign_scenario(int32_t num_servers, int32_t num_workers, uint64_t lo, uint64_t hi, char* out,
                               int64_t cap, int64_t* len);
 }
@@ -76,6 +77,12 @@ int main(int argc, char** argv) {
     int64_t bytes = 0;
     report("van ring (in-process)", psh_van_ring(4, 0, 0, 2000, &bytes));
     report("van ring (tcp)", psh_van_ring(3, 1, 26500 + (int)(getpid() % 2000), 2000, &bytes));
+  }
+  if (want("kvmap")) {
+    std::vector<double> vals(16);
+    int rc = psh_run_kvmap_scenario(16, vals.data());
+    for (double v : vals) if (!rc && v != 7.0) rc = 1;
+    report("kvmap operators in order", rc);
   }
   if (want("reassign")) {
     std::vector<char> buf(1 << 16);

@@ -645,6 +645,69 @@ PSH_API int psh_run_heartbeat_scenario(int32_t interval_s, int32_t run_ms, int32
   return put(rep, out, cap, len);
 }
 
+// ---- KVMap: per-key operators applied in timestamp order ------------------------------------------------
+namespace {
+class MapServerApp : public App {
+ public:
+  explicit MapServerApp(const string& name) : App(name), map_("m", name) {}
+  ~MapServerApp() { stopExecutor(); }
+  KVMap<Key, double> map_;
+};
+class MapWorkerApp : public App {
+ public:
+  MapWorkerApp(const string& name, int n, std::vector<double>* out) : App(name), map_("m", name), n_(n), out_(out) {}
+  ~MapWorkerApp() { stopExecutor(); }
+  void run() override {
+    SArray<Key> key;
+    for (int k = 0; k < n_; ++k) key.pushBack(spreadKey(k, n_));
+    const std::pair<Operator, double> steps[] = {{PLUS, 5}, {TIMES, 3}, {MINUS, 1}, {DIVIDE, 2}};
+    int t = -1;
+    for (const auto& st : steps) {   // not waited for one by one: the executor keeps the order
+      MessagePtr push(new Message(kServerGroup));
+      push->setKey(key);
+      push->addValue(SArray<double>(key.size(), st.second));
+      KVMap<Key, double>::set(push).set_op(st.first);
+      t = map_.push(push);
+    }
+    map_.waitOutMsg(kServerGroup, t);
+    MessagePtr pull(new Message(kServerGroup));
+    pull->setKey(key);
+    map_.waitOutMsg(kServerGroup, map_.pull(pull));
+    MessagePtr mine(new Message(kServerGroup));   // read my cached copy back through getValue
+    mine->setKey(key);
+    map_.getValue(mine);
+    SArray<double> v(mine->value[0]);
+    out_->assign(v.begin(), v.end());
+  }
+  KVMap<Key, double> map_;
+  int n_;
+  std::vector<double>* out_;
+};
+}  // namespace
+
+// 2 servers hold an (initially empty) KVMap; one worker pushes +5, *3, -1, /2 on n spread keys and
+// pulls: every value must be ((0 + 5) * 3 - 1) / 2 = 7
+PSH_API int psh_run_kvmap_scenario(int32_t n_keys, double* out_vals) {
+  std::vector<double> got;
+  MiniCluster c;
+  c.add(NodeView::SCHEDULER, "H");
+  c.add(NodeView::SERVER, "S0");
+  c.add(NodeView::SERVER, "S1");
+  c.add(NodeView::WORKER, "W0");
+  auto factory = [&](const string& name, const string&) -> App* {
+    Node me = Postoffice::current().myNode();
+    if (me.role() == NodeView::SERVER) return new MapServerApp(name);
+    if (me.role() == NodeView::WORKER) return new MapWorkerApp(name, n_keys, &got);
+    return new App(name);
+  };
+  c.launch(2, 1, 0, 0, factory);
+  string stuck = c.join(30);
+  if (!stuck.empty()) return fail("nodes did not stop: " + stuck);
+  if ((int)got.size() != n_keys) return fail("worker read " + to_string(got.size()) + " values");
+  for (int i = 0; i < n_keys; ++i) out_vals[i] = got[i];
+  return 0;
+}
+
 // ---- van ring / key-range reassignment (ref src/test/van_test.cc, reassign_server_key_range.cc) -------
 // n vans in one process; a message with a key array and a value array of `payload` elements goes
 // around the ring n times (every van forwards what it receives to its successor).  Returns 0 when

@@ -431,13 +431,14 @@ class KVMap : public SharedParameter<K> {
     SArray<V> value(msg->value[0]);
     Operator op = msg->task.shared_para().op();
     Lock l(mu_);
-    auto& rep = replica_[msg->sender];
+    // keyed by the owner's key range (a replacement node asks for the range, not for a node id)
+    auto& rep = replica_[Range<K>(msg->task.key_range().template to<K>()).begin()];
     for (size_t i = 0; i < key.size(); ++i) compAssOp(rep[key[i]], value[i], op);
   }
   void getReplica(const MessagePtr& msg) override {
     Lock l(mu_);
     std::map<K, V> sorted;
-    auto it = replica_.find(msg->recver);
+    auto it = replica_.find(Range<K>(msg->task.key_range().template to<K>()).begin());
     if (it != replica_.end()) sorted.insert(it->second.begin(), it->second.end());
     SArray<K> k;
     SArray<V> v;
@@ -463,7 +464,7 @@ class KVMap : public SharedParameter<K> {
  protected:
   std::mutex mu_;
   std::unordered_map<K, V> data_;
-  std::map<NodeID, std::unordered_map<K, V>> replica_;
+  std::map<K, std::unordered_map<K, V>> replica_;
 };
 
 // =================================================================================================

@@ -261,3 +261,10 @@ def selftest(area: str = "all") -> int:
     n = C.c_int32(0)
     hcheck(_lib().psh_selftest(area.encode(), C.byref(n)))
     return int(n.value)
+
+
+def run_kvmap_scenario(n_keys: int = 16) -> np.ndarray:
+    """KVMap on 2 servers: one worker pushes +5, *3, -1, /2 on every key and pulls (expects 7)."""
+    out = np.zeros(n_keys, dtype=np.float64)
+    hcheck(_lib().psh_run_kvmap_scenario(n_keys, _ptr(out, C.c_double)))
+    return out

@@ -186,3 +186,9 @@ def test_native_util_checks(area):
     assert host.selftest(area) >= 3
     with pytest.raises(Exception):
         host.selftest("no-such-area")
+
+
+def test_kvmap_operators_apply_in_order():
+    """KVMap (ref src/parameter/kv_map.h): PLUS, TIMES, MINUS, DIVIDE pushed back to back without
+    waiting are applied in timestamp order on every shard"""
+    np.testing.assert_allclose(host.run_kvmap_scenario(16), 7.0)

@@ -93,4 +93,4 @@ def test_selftest_binary():
     assert exe.exists()
     r = subprocess.run([str(exe), "all"], capture_output=True, text=True, timeout=170)
     assert r.returncode == 0 and "0 failure(s)" in r.stderr, r.stderr[-3000:]
-    assert r.stderr.count("\nok ") + r.stderr.startswith("ok ") >= 11
+    assert r.stderr.count("\nok ") + r.stderr.startswith("ok ") >= 12
