@@ -43,7 +43,12 @@ typedef struct psb_darlin_ctrl {
                                 reference leaves them NaN forever, default 0 */
   int32_t server_cta_keys;   /* persistent kernel: steps with at most this many shard keys are
                                 updated by one CTA (0 = default 4096); larger ones by the grid */
-  int32_t flags;             /* bit 0: do not prefetch the next step's CSC ranges into L2 */
+  int32_t flags;             /* persistent pass kernel only.  1: do not prefetch the next step's CSC
+                              * ranges into L2; 4: fill CTAs one after the other with segments instead
+                              * of dealing segments round robin over all CTAs.  8, 16, 32 are timing
+                              * experiments that produce WRONG results (skip the margin updates / the
+                              * margin gather + arithmetic / the arithmetic only), see
+                              * profiles/README.md "Where a step goes". */
   int32_t reserved;
 } psb_darlin_ctrl;
 
