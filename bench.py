@@ -209,7 +209,15 @@ def main() -> None:
     dev_ms, span_ms, wall_ms, ker_ms = times.tolist()
     # time to objective: keep going (untimed for the headline) until the reference's stopping rule
     it = args.warmup + args.steps
-    while converged_at is None and it < args.max_pass:
+
+    def keep_going():
+        go = converged_at is None and it < args.max_pass
+        if world > 1:  # every rank sees the same objective, but a collective decision cannot diverge
+            flag = torch.tensor([int(go)], dtype=torch.int64, device=dev)
+            dist.broadcast(flag, 0)
+            go = bool(flag.item())
+        return go
+    while keep_going():
         one_pass(it)
         it += 1
     n_conv = (converged_at + 1) if converged_at is not None else len(pass_wall)
