@@ -77,3 +77,16 @@ def test_generators_are_seeded_and_shaped():
     for grp, d in c.items():
         assert d.vals is None and d.n_rows == 300
         assert torch.all((d.keys >> 54) == grp)          # group id in the top 10 bits (TERAFEA layout)
+
+
+def test_multi_rank_protocol_model():
+    """tools/protocol_check.py: random interleavings of the landing-slot / mirror protocol of the
+    multi-rank Darlin pass hold its invariants, and the checker notices when the protocol is broken."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("protocol_check", f"{ROOT}/tools/protocol_check.py")
+    pc = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(pc)
+    assert pc.check(ranks=3, keys=12, blocks=4, passes=4, schedules=60, verbose=False) == 0
+    assert pc.check(ranks=2, keys=9, blocks=3, passes=5, schedules=60, seed=7, verbose=False) == 0
+    assert pc.check(schedules=40, mutate="no_reset", verbose=False) > 0          # consumer forgets to reset a slot
+    assert pc.check(schedules=120, mutate="no_republish", verbose=False) > 0     # owner forgets to re-send the mark
