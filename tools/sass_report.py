@@ -16,7 +16,8 @@ KERNELS = {
     "k_darlin_passILb0ELb1": "k_darlin_pass_single.sass",
     "k_darlin_passILb0ELb0": "k_darlin_pass_multi.sass",
     "k_sgd_worker_step": "k_sgd_worker_step.sass",
-    "k_sgd_server": "k_sgd_server.sass",
+    "k_sgd_server_all": "k_sgd_server_all.sass",
+    "k_sgd_serverE": "k_sgd_server.sass",
     "k_kv_bulk_send": "k_kv_bulk_send.sass",
     "k_kv_push_add": "k_kv_push_add.sass",
 }
@@ -42,7 +43,9 @@ def main() -> int:
         for key, fn in KERNELS.items():
             if key in name:
                 body = f
-                (OUT / fn).write_text("Function : " + body)
+                # keep address + instruction, drop the hex encodings (8x smaller listings)
+                slim = [re.sub(r"\s*/\* 0x[0-9a-f]{16} \*/\s*$", "", ln) for ln in body.splitlines()]
+                (OUT / fn).write_text("Function : " + "\n".join(ln for ln in slim if ln.strip()) + "\n")
                 ins = re.findall(r"^\s+/\*[0-9a-f]+\*/\s+(.*?);", body, flags=re.M)
                 cnt = collections.Counter()
                 for i in ins:
