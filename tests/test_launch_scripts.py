@@ -94,3 +94,18 @@ def test_selftest_binary():
     r = subprocess.run([str(exe), "all"], capture_output=True, text=True, timeout=170)
     assert r.returncode == 0 and "0 failure(s)" in r.stderr, r.stderr[-3000:]
     assert r.stderr.count("\nok ") + r.stderr.startswith("ok ") >= 12
+
+
+def test_gzip_text_input(tmp_path):
+    """*.gz training files are read through zlib (ref src/util/file.cc gz support)"""
+    import gzip
+    import torch
+    from parameter_server_b200.utils.data_io import load_slot_data
+    from parameter_server_b200.utils.synthetic import make_rcv1_like, write_libsvm
+    shard = make_rcv1_like(150, 60, 6.0, seed=8)
+    write_libsvm(shard, str(tmp_path / "p.txt"))
+    with open(tmp_path / "p.txt", "rb") as f, gzip.open(tmp_path / "p.txt.gz", "wb") as g:
+        g.write(f.read())
+    os.remove(tmp_path / "p.txt")
+    g = load_slot_data(f'format: TEXT text: LIBSVM file: "{tmp_path}/p.txt.gz"', str(tmp_path / "cache_"))[1]
+    assert g.n_rows == 150 and g.nnz == shard.nnz and torch.equal(g.keys, shard.keys)
