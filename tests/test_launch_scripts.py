@@ -109,3 +109,20 @@ def test_gzip_text_input(tmp_path):
     os.remove(tmp_path / "p.txt")
     g = load_slot_data(f'format: TEXT text: LIBSVM file: "{tmp_path}/p.txt.gz"', str(tmp_path / "cache_"))[1]
     assert g.n_rows == 150 and g.nnz == shard.nnz and torch.equal(g.keys, shard.keys)
+
+
+def test_observability_flags(tmp_path):
+    """-print_van (message trace per node), -traffic_statistics (bytes at exit), -log_to_file
+    (ref SURVEY 5.1 / 5.5: van.cc, postoffice.cc)"""
+    env = dict(os.environ, PS_BASE_PORT=str(random.randint(20000, 40000)))
+    r = subprocess.run([str(ROOT / "script" / "local.sh"), str(HELLO), "1", "2", "-print_van", "-traffic_statistics",
+                        "-log_to_file"], cwd=tmp_path, env=env, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    names = sorted(os.listdir(tmp_path))
+    for node in ("H", "S0", "W0", "W1"):
+        assert f"van_{node}" in names and f"log_{node}" in names, names
+    trace = (tmp_path / "van_W0").read_text()
+    assert "SND" in trace and "RCV" in trace and "shared_para { cmd: PULL }" in trace
+    logs = "".join((tmp_path / f"log_{n}").read_text() for n in ("H", "S0", "W0", "W1")) + r.stderr
+    assert logs.count("Gbyte") >= 4            # one traffic line per node
+    _check_hello(r.stdout)
