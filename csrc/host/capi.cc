@@ -1025,4 +1025,5 @@ static void psh_crash_handler(int sig) {
 PSH_API void psh_install_crash_handler() {
   signal(SIGSEGV, psh_crash_handler);
   signal(SIGABRT, psh_crash_handler);
+  signal(SIGFPE, psh_crash_handler);
 }

@@ -78,6 +78,7 @@ class CountMin : public Sketch {
     for (size_t i = 0; i < key.size(); ++i) insert(key[i], count[i]);
   }
   void insert(const K& key, const V& count) {
+    CHECK_GT(n_, 0) << "CountMin::insert before resize()";
     uint32 h = hash(key);
     const uint32 delta = (h >> 17) | (h << 15);
     for (int j = 0; j < k_; ++j) {
@@ -88,6 +89,7 @@ class CountMin : public Sketch {
   }
   V query(const K& key) const {
     V res = 0;
+    if (n_ == 0) return res;  // nothing was ever counted (a query may overtake every insert)
     uint32 h = hash(key);
     const uint32 delta = (h >> 17) | (h << 15);
     for (int j = 0; j < k_; ++j) {

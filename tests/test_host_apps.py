@@ -188,3 +188,19 @@ def test_load_slot_data_roundtrip(dataset, tmp_path):
     # second load hits the cache and returns the same arrays
     g2 = load_slot_data(conf, str(tmp_path / "cache_"))[1]
     assert torch.equal(g2.keys, g.keys) and torch.equal(g2.row_ptr, g.row_ptr)
+
+
+def test_shipped_ctr_configs_run_unchanged(tmp_path, monkeypatch):
+    """example/linear/ctr/{batch,online}_l1lr.conf (SPARSE_BINARY text with feature groups, prior groups,
+    tail filter, max_block_delay 8 / FTRL with ignore_feature_group) run as they are on a CPU cluster."""
+    from parameter_server_b200.utils.synthetic import make_ctr_like, write_ps_sparse_binary
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    os.makedirs(tmp_path / "data" / "ctr" / "train")
+    for p in range(4):
+        write_ps_sparse_binary(make_ctr_like(600, seed=0, shard=p), str(tmp_path / "data" / "ctr" / "train" / f"part-{p:03d}"))
+    monkeypatch.chdir(tmp_path)
+    rep = _report(host.run_cluster(open(f"{root}/example/linear/ctr/batch_l1lr.conf").read(), 2, 2))
+    assert len(rep) >= 5 and rep[-1]["obj"] < rep[0]["obj"] and rep[-1]["nnz"] > 0
+    assert any(f.startswith("ctr_batch") or "_S" in f for f in os.listdir(tmp_path / "model"))
+    loss, auc = map(float, host.run_cluster(open(f"{root}/example/linear/ctr/online_l1lr.conf").read(), 2, 2).split())
+    assert math.isfinite(loss) and 0.0 <= auc <= 1.0
