@@ -204,3 +204,23 @@ def test_shipped_ctr_configs_run_unchanged(tmp_path, monkeypatch):
     assert any(f.startswith("ctr_batch") or "_S" in f for f in os.listdir(tmp_path / "model"))
     loss, auc = map(float, host.run_cluster(open(f"{root}/example/linear/ctr/online_l1lr.conf").read(), 2, 2).split())
     assert math.isfinite(loss) and 0.0 <= auc <= 1.0
+
+
+def test_shipped_rcv1_configs_train_then_evaluate(tmp_path, monkeypatch):
+    """example/linear/rcv1: batch_l1lr.conf -> eval_batch.conf and online_l1lr.conf -> eval_online.conf,
+    all four files unchanged, on synthetic data laid out the way download.sh would leave it."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for split, n, base in (("train", 4, 0), ("test", 1, 1000)):
+        os.makedirs(tmp_path / "data" / "rcv1" / split)
+        for p in range(n):
+            write_libsvm(make_rcv1_like(1200, 400, 16.0, seed=0, shard=p + base),
+                         str(tmp_path / "data" / "rcv1" / split / f"part-{p:03d}"))
+    monkeypatch.chdir(tmp_path)
+    conf = lambda name: open(f"{root}/example/linear/rcv1/{name}.conf").read()  # noqa: E731
+    rep = _report(host.run_cluster(conf("batch_l1lr"), 2, 2))
+    assert rep[-1]["obj"] < rep[0]["obj"]
+    auc, acc, n = host.run_cluster(conf("eval_batch"), 0, 0).split()
+    assert int(n) == 1200 and float(auc) > 0.8
+    host.run_cluster(conf("online_l1lr"), 2, 2)
+    auc, acc, n = host.run_cluster(conf("eval_online"), 0, 0).split()
+    assert int(n) == 1200 and float(auc) > 0.7
