@@ -204,6 +204,11 @@ def test_shipped_ctr_configs_run_unchanged(tmp_path, monkeypatch):
     assert any(f.startswith("ctr_batch") or "_S" in f for f in os.listdir(tmp_path / "model"))
     loss, auc = map(float, host.run_cluster(open(f"{root}/example/linear/ctr/online_l1lr.conf").read(), 2, 2).split())
     assert math.isfinite(loss) and 0.0 <= auc <= 1.0
+    os.makedirs(tmp_path / "data" / "ctr" / "test")
+    write_ps_sparse_binary(make_ctr_like(500, seed=0, shard=1000), str(tmp_path / "data" / "ctr" / "test" / "part-000"))
+    for name in ("eval_batch", "eval_online"):
+        auc, acc, n = host.run_cluster(open(f"{root}/example/linear/ctr/{name}.conf").read(), 0, 0).split()
+        assert int(n) == 500 and 0.0 <= float(auc) <= 1.0 and float(acc) > 0.5
 
 
 def test_shipped_rcv1_configs_train_then_evaluate(tmp_path, monkeypatch):
