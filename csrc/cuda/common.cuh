@@ -110,8 +110,14 @@ __device__ __forceinline__ void grid_wait(const uint32_t* ctr, uint32_t target) 
   if (threadIdx.x == 0) spin_gpu_ge(ctr, target);
   __syncthreads();
 }
+// Bounded like every other device-side wait on a peer: ~10 s of polling, then trap (the launch
+// fails with an error instead of hanging the GPU behind a dead or late peer).
 __device__ __forceinline__ void spin_until_ge(const uint64_t* flag, uint64_t want) {
-  while (ld_acquire_sys(flag) < want) { __nanosleep(20); }
+  uint32_t spins = 0;
+  while (ld_acquire_sys(flag) < want) {
+    __nanosleep(20);
+    if (++spins > (1u << 27)) __trap();
+  }
 }
 
 // NaN-as-signal ("inactive coordinate"), reference src/filter/sparse_filter.h:5-24

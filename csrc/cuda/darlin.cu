@@ -552,41 +552,36 @@ __device__ __forceinline__ double update_coord(const psb_darlin_server& S, const
   return vio;
 }
 
-// ---- fused multi-rank pass: landing slots that are their own arrival flags --------------------
-// A worker's push is two plain 8-byte peer stores (g, u).  The server thread of a coordinate
-// polls the slots of the workers that hold the column (S.has) until neither is the EMPTY
-// pattern, stores EMPTY back, reduces in worker order (bit-reproducible), applies the proximal
-// update and stores (w, dw) into every such worker's mirror.  No ticket, no push flag, no
-// system fence on the push side: the NVLink flight of the pushes overlaps the local grid
-// barrier that separates the margin reads of phase 1 from the margin updates of phase 3.
-// A slot is written at most once per visit of its block, and two visits are separated by
-// grid barriers on both sides, so the stored-back EMPTY is in L2 long before the next push.
-constexpr unsigned long long kEmptySlot = PSB_DARLIN_EMPTY_SLOT;
+// ---- fused multi-rank pass: one NVLink flight per step, replicated coordinate update ----------
+// Every rank keeps a replica of (w, delta, active bit) of every column of the global dictionary.
+// A worker's push of column j is one tagged 32-byte entry {g, u} stored into the landing table of
+// every rank that needs it (the ranks that hold nonzeros of j and the owner of j): lane q of the
+// pushing warp stores to rank q, so the N peer stores leave together.  In phase 3 every warp
+// that works on a segment of column j polls, in its OWN memory, the entries of the workers
+// that hold j (lane r polls worker r), sums them in worker order and applies the proximal update
+// itself.  All ranks run the same instructions on the same bits, so the replicas stay identical
+// (ref darlin.h:206-246 is evaluated N times instead of once plus a broadcast); the owner's copy
+// is the authoritative shard that is evaluated and saved.  Compared with owner-computes this
+// removes the owner's serial shard phase and the second NVLink flight (owner -> holders) from
+// every step; it costs N-1 more 32-byte stores per column and step.
+//
+// An entry is {g.lo, tag, g.hi, tag | u.lo, tag, u.hi, tag}: every 8-byte half carries the low
+// word of the step's sequence number, so a reader that finds the four tags equal to the step
+// it is in holds a complete, fresh (g, u) - no flag, no fence, no reset.  Only 8-byte
+// single-copy atomicity of peer stores is assumed.  Entries are double-buffered by step parity
+// and a writer starts step s only after every peer finished step s-2 (W.done_local, stored by
+// the peers after their last barrier of a step), so an unread entry is never overwritten.
 constexpr uint32_t kSpinLimit = 1u << 26;  // ~10 s of polling: trap instead of hanging the GPU
 
-__device__ __forceinline__ double poll_slot(double* slot) {
-  unsigned long long bits;
-  uint32_t spins = 0;
-  while ((bits = *reinterpret_cast<volatile unsigned long long*>(slot)) == kEmptySlot) {
-    if (++spins > kSpinLimit) __trap();
-  }
-  return __longlong_as_double((long long)bits);
-}
-
-// A mirror entry is 32 bytes: {w.lo, seq, w.hi, seq} {dw.lo, seq, dw.hi, seq}.  Every 8-byte half
-// carries the low word of the step's sequence number, so a reader that finds the four tags
-// equal to the step it is in holds a complete, fresh (w, dw): no version flag, no system
-// fence, no reset (the next visit of the key carries another tag).  Only 8-byte single-copy
-// atomicity of the peer stores is assumed.
-__device__ __forceinline__ void mirror_store(void* entry, double w, double dw, uint32_t tag) {
-  const unsigned long long a = (unsigned long long)__double_as_longlong(w);
-  const unsigned long long b = (unsigned long long)__double_as_longlong(dw);
-  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %2};" ::"l"(entry), "r"((uint32_t)a),
-               "r"(tag), "r"((uint32_t)(a >> 32)) : "memory");
+__device__ __forceinline__ void entry_store(void* entry, double a, double b, uint32_t tag) {
+  const unsigned long long x = (unsigned long long)__double_as_longlong(a);
+  const unsigned long long y = (unsigned long long)__double_as_longlong(b);
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %2};" ::"l"(entry), "r"((uint32_t)x),
+               "r"(tag), "r"((uint32_t)(x >> 32)) : "memory");
   asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %2};" ::"l"((char*)entry + 16),
-               "r"((uint32_t)b), "r"(tag), "r"((uint32_t)(b >> 32)) : "memory");
+               "r"((uint32_t)y), "r"(tag), "r"((uint32_t)(y >> 32)) : "memory");
 }
-__device__ __forceinline__ void mirror_poll(const void* entry, uint32_t tag, double& w, double& dw) {
+__device__ __forceinline__ void entry_poll(const void* entry, uint32_t tag, double& a, double& b) {
   uint32_t a0, a1, a2, a3, b0, b1, b2, b3, spins = 0;
   for (;;) {
     asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
@@ -596,87 +591,12 @@ __device__ __forceinline__ void mirror_poll(const void* entry, uint32_t tag, dou
     if (a1 == tag && a3 == tag && b1 == tag && b3 == tag) break;
     if (++spins > kSpinLimit) __trap();
   }
-  w = __longlong_as_double((long long)((unsigned long long)a0 | ((unsigned long long)a2 << 32)));
-  dw = __longlong_as_double((long long)((unsigned long long)b0 | ((unsigned long long)b2 << 32)));
+  a = __longlong_as_double((long long)((unsigned long long)a0 | ((unsigned long long)a2 << 32)));
+  b = __longlong_as_double((long long)((unsigned long long)b0 | ((unsigned long long)b2 << 32)));
 }
-
-// One group of `gs` lanes (the power of two >= n_workers) per coordinate: lane r polls worker
-// r's slots, every lane forms the same fixed-order sums and the same update, lane r stores
-// the result into worker r's mirror, lane 0 keeps the shard.
-__device__ __forceinline__ double server_phase_direct(const psb_darlin_server& S, const ServerHyper& h,
-                                                      const StepPlan& plan, int bps, int64_t tid,
-                                                      int64_t nthreads, uint32_t tag) {
-  const int64_t total = plan.pref[bps];
-  int gs = 1;
-  while (gs < S.n_workers) gs <<= 1;
-  const int lane = threadIdx.x & 31;
-  const int r = lane & (gs - 1);
-  const uint32_t gmask = (gs == 32 ? 0xffffffffu : ((1u << gs) - 1u)) << (lane & ~(gs - 1));
-  const int64_t grp = tid / gs, ngrp = nthreads / gs;
-  double vio_max = 0;
-  for (int64_t v = grp; v < total; v += ngrp) {
-    const int q = locate(plan, bps, v);
-    const int64_t k = plan.first[q] + (v - plan.pref[q]);
-    const uint32_t aw = __ldcg(S.active + (k >> 5));
-    const double w = __ldcg(S.w + k);
-    const double dl = __ldcg(S.delta + k);
-    const uint32_t has = __ldg(S.has + k);
-    // a worker pushes exactly when its copy of the active bit is set, and the two copies
-    // change together (the mark published below clears the workers' bits in their phase 3)
-    if (!(aw >> (k & 31) & 1u)) continue;
-    const bool mine = r < S.n_workers && (has >> r & 1u);
-    double gv = 0, uv = 0;
-    if (mine) {
-      const int64_t at = (int64_t)r * S.land_cap + k;
-      gv = poll_slot(S.land_g + at);
-      uv = poll_slot(S.land_u + at);
-      *reinterpret_cast<unsigned long long*>(S.land_g + at) = kEmptySlot;
-      *reinterpret_cast<unsigned long long*>(S.land_u + at) = kEmptySlot;
-    }
-    double g = 0, u = 0;
-    for (int i = 0; i < S.n_workers; ++i) {  // worker order: bit-reproducible
-      g += __shfl_sync(gmask, gv, i, gs);
-      u += __shfl_sync(gmask, uv, i, gs);
-    }
-    double w_new = nan_mark(), dw = 0;
-    if (is_marked(w)) {  // filtered earlier and not revived: keep both bit copies clear
-      if (r == 0) bit_clear_atomic(S.active, k);
-    } else {
-      u = u / h.eta + 1e-10;
-      const double g_pos = g + h.lambda, g_neg = g - h.lambda;
-      double d = -w, vio = 0;
-      bool filtered = false;
-      if (w == 0) {
-        if (g_pos < 0) {
-          vio = -g_pos;
-        } else if (g_neg > 0) {
-          vio = g_neg;
-        } else if (g_pos > h.thr && g_neg < -h.thr) {
-          filtered = true;
-        }
-      }
-      if (filtered) {
-        if (r == 0) bit_clear_atomic(S.active, k);
-      } else {
-        vio_max = fmax(vio_max, vio);
-        if (g_pos <= u * w) {
-          d = -g_pos / u;
-        } else if (g_neg >= u * w) {
-          d = -g_neg / u;
-        }
-        d = fmin(dl, fmax(-dl, d));
-        if (r == 0) S.delta[k] = fmin(h.delta_max, 2 * fabs(d) + .1);
-        w_new = w + d;
-        dw = w_new - w;
-      }
-      if (r == 0) {
-        S.w[k] = w_new;
-        S.dw[k] = dw;
-      }
-    }
-    if (mine) mirror_store(S.mir[r] + 32 * k, w_new, dw, tag);  // peer store when r != rank
-  }
-  return vio_max;
+__device__ __forceinline__ int64_t entry_index(const psb_darlin_worker& W, uint32_t tag, int from,
+                                               int64_t j) {
+  return (((int64_t)(tag & 1u) * W.n_workers + from) * W.n_cols + j) * 32;
 }
 
 __device__ __forceinline__ void spin_flag_ge(const uint64_t* flag, uint64_t want) {
@@ -687,7 +607,7 @@ __device__ __forceinline__ void spin_flag_ge(const uint64_t* flag, uint64_t want
   }
 }
 
-// Everything about one segment that does not change during a pass, held in registers.  The
+// Everything about one segment that does not change during a step, held in registers.  The
 // persistent kernel stages the first segment of every warp for step s+1 while it waits on the
 // last barrier of step s, and keeps it from phase 1 to phase 3 of the step: what remains on the
 // critical path after a barrier is one level of loads of mutable state (margins, trust region,
@@ -697,11 +617,18 @@ struct SegRegs {
   int64_t j, beg, off;  // column, first entry, coordinate offset inside the owner's shard
   int len, nseg, sc, owner;  // entries; segments of the column; my position among them; owner rank
   bool first, single;
+  uint32_t has;         // ranks that hold nonzeros of the column (multi-rank pass)
   uint32_t idx[kUnroll];
   float sv[kUnroll];
 };
+// the coordinate's state as phase 1 saw it, carried to phase 3 (multi-rank pass): phase 3 of the
+// column's first segment overwrites the state while the other segments still need the old one
+struct Carry {
+  double w, dl;
+  bool act;
+};
 
-template <bool BINARY>
+template <bool BINARY, bool SINGLE>
 __device__ __forceinline__ void stage_segment(SegRegs& R, const psb_darlin_worker& W,
                                               const StepPlan& plan, int bps, int64_t v, int lane) {
   R.v = v;
@@ -716,6 +643,7 @@ __device__ __forceinline__ void stage_segment(SegRegs& R, const psb_darlin_worke
   }
   R.owner = __ldg(W.col_owner + m.j);
   R.off = __ldg(W.col_off + m.j);
+  R.has = SINGLE ? 1u : __ldg(W.col_has + m.j);
   R.nseg = 1; R.sc = 0;
   if (!m.single) {
     const int64_t cs = __ldg(W.col_seg + m.j);
@@ -730,11 +658,13 @@ __device__ __forceinline__ void stage_segment(SegRegs& R, const psb_darlin_worke
   }
 }
 
-__device__ __forceinline__ void push_staged(const psb_darlin_worker& W, const SegRegs& R, double g,
-                                            double u) {
-  const int64_t at = (int64_t)W.rank * W.land_cap[R.owner] + R.off;
-  W.land_g[R.owner][at] = g;  // peer store when owner != rank
-  W.land_u[R.owner][at] = u;
+// lane q stores the column's (g, u) into rank q's landing table when rank q holds the column
+// or owns it; every lane holds the same g, u
+__device__ __forceinline__ void push_entries(const psb_darlin_worker& W, const SegRegs& R, double g,
+                                             double u, uint32_t tag, int lane) {
+  const uint32_t targets = R.has | (1u << R.owner);
+  if (lane < W.n_workers && (targets >> lane & 1u))
+    entry_store(W.land2[lane] + entry_index(W, tag, W.rank, R.j), g, u, tag);  // peer store
 }
 
 // ---- batched fp64 exp / reciprocal ----------------------------------------------------------
@@ -798,31 +728,34 @@ __device__ __forceinline__ void rcp_batch(double (&a)[N]) {  // a >= 1
   for (int i = 0; i < N; ++i) a[i] = r[i];
 }
 
-// time stamp that cannot be hoisted above the value it names (profiling builds of the pass only)
-__device__ __forceinline__ unsigned long long stamp_after(double dep) {
-  unsigned long long t;
-  asm volatile("{ .reg .f64 t; mov.f64 t, %1; mov.u64 %0, %%globaltimer; }" : "=l"(t) : "d"(dep) : "memory");
-  return t;
-}
-
+// Phase 1 of one segment.  SINGLE: the warp that completes a column applies the shard update at
+// once and returns its KKT violation.  Otherwise the completed (g, u) is pushed to the ranks that
+// need it and the coordinate's state is returned in `C` for phase 3.
 template <bool BINARY, bool SINGLE>
 __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const psb_darlin_server& S,
                                                const ServerHyper& h, const SegRegs& R, int lane,
-                                               const double* __restrict__ exp_tab,
-                                               unsigned long long* tp = nullptr, int dbg = 0) {
-  unsigned long long t0 = 0, t1 = 0, t2 = 0, t3 = 0, t4 = 0;
-  if (tp) t0 = stamp_after(0.0);
-  // one latency level: active word, trust region, the margins and (single rank) the coordinate
+                                               const double* __restrict__ exp_tab, uint32_t tag,
+                                               Carry& C) {
+  // one latency level: active word, trust region, the margins and the coordinate
   const uint32_t aw = __ldcg(W.active + (R.j >> 5));
   double d = __ldcg(W.delta + R.j);
   double sw = 0, sdl = 0;
   uint32_t saw = 0;
-  if (SINGLE && lane == 0) {  // any segment may turn out to be the one that reduces the column
-    sw = __ldcg(S.w + R.off);
-    sdl = __ldcg(S.delta + R.off);
-    saw = __ldcg(S.active + (R.off >> 5));
+  if (SINGLE) {
+    if (lane == 0) {  // any segment may turn out to be the one that reduces the column
+      sw = __ldcg(S.w + R.off);
+      sdl = __ldcg(S.delta + R.off);
+      saw = __ldcg(S.active + (R.off >> 5));
+    }
+  } else {
+    C.w = __ldcg(W.w + R.j);
+    C.dl = d;
+    // a weight that was KKT-filtered stays marked after a filter reset:
+    // nothing is pushed or pulled for it, its bits stay as they are
+    C.act = (aw >> (R.j & 31) & 1u) && !is_marked(C.w);
+    if (!C.act || R.len == 0) return 0;  // a rank without nonzeros in the column pushes nothing
   }
-  if (!(aw >> (R.j & 31) & 1u)) return 0;  // inactive column: nothing is pushed
+  if (SINGLE && !(aw >> (R.j & 31) & 1u)) return 0;  // inactive column: nothing is pushed
   if (BINARY) d = exp(d);
   double g = 0, u = 0;
   uint32_t idx[kUnroll];
@@ -830,7 +763,6 @@ __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const
 #pragma unroll
   for (int k = 0; k < kUnroll; ++k) { idx[k] = R.idx[k]; sv[k] = R.sv[k]; }
   for (int base = 0; base < R.len; base += 32 * kUnroll) {
-    if (dbg & 16) { g = 1e-3 * sv[0]; u = 1.0; break; }  // timing experiment only
     if (base > 0) {
 #pragma unroll
       for (int k = 0; k < kUnroll; ++k) {
@@ -847,12 +779,6 @@ __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const
     double zz[kUnroll];
 #pragma unroll
     for (int k = 0; k < kUnroll; ++k) zz[k] = idx[k] != 0xffffffffu ? __ldcg(W.z + idx[k]) : 0.0;
-    if (tp && base == 0) t1 = stamp_after(zz[0] + zz[1] + zz[2] + zz[3] + d + sw + sdl);
-    if (dbg & 32) {  // timing experiment only: the gather without the arithmetic
-#pragma unroll
-      for (int k = 0; k < kUnroll; ++k) { g -= 1e-3 * zz[k] + 0.5 * (double)sv[k]; u += 1.0; }
-      continue;
-    }
     // branch-free over the batch so the four exp/divide chains interleave (fp64 latency bound);
     // a padding entry has x == 0 and contributes exactly nothing
     double tau[kUnroll], x[kUnroll], cv[kUnroll];
@@ -873,14 +799,13 @@ __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const
   }
   g = warp_sum(g);
   u = warp_sum(u);
-  if (tp) t2 = stamp_after(g + u);
   double vio = 0;
   if (R.single) {
-    if (lane == 0) {
-      if (SINGLE) vio = update_coord(S, h, R.off, g, u, sw, sdl, saw >> (R.off & 31) & 1u);
-      else push_staged(W, R, g, u);
+    if (SINGLE) {
+      if (lane == 0) vio = update_coord(S, h, R.off, g, u, sw, sdl, saw >> (R.off & 31) & 1u);
+    } else {
+      push_entries(W, R, g, u, tag, lane);
     }
-    if (tp && lane == 0) { tp[0] += t1 - t0; tp[1] += t2 - t1; tp[5] += 1; }
     return vio;
   }
   int old = 0;
@@ -891,8 +816,6 @@ __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const
     old = (int)atom_add_acqrel_gpu(reinterpret_cast<uint32_t*>(W.col_cnt + R.j), 1u);
   }
   old = __shfl_sync(FULL, old, 0);
-  if (tp) t3 = stamp_after((double)old);
-  if (tp && lane == 0) { tp[0] += t1 - t0; tp[1] += t2 - t1; tp[2] += t3 - t2; tp[5] += 1; }
   if (old == R.nseg - 1) {
     const int64_t v0 = R.v - R.sc;
     double sg = 0, su = 0;
@@ -902,15 +825,28 @@ __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const
     }
     sg = warp_sum(sg);
     su = warp_sum(su);
-    if (tp) t4 = stamp_after(sg + su);
-    if (lane == 0) {
-      if (SINGLE) vio = update_coord(S, h, R.off, sg, su, sw, sdl, saw >> (R.off & 31) & 1u);
-      else push_staged(W, R, sg, su);
-      W.col_cnt[R.j] = 0;
+    if (SINGLE) {
+      if (lane == 0) vio = update_coord(S, h, R.off, sg, su, sw, sdl, saw >> (R.off & 31) & 1u);
+    } else {
+      push_entries(W, R, sg, su, tag, lane);
     }
-    if (tp && lane == 0) { tp[3] += t4 - t3; tp[4] += stamp_after(vio) - t4; tp[6] += 1; }
+    if (lane == 0) W.col_cnt[R.j] = 0;
   }
   return vio;
+}
+
+// Segments beyond a warp's first one of a step (steps with more segments than resident warps)
+// cannot keep their phase-1 state in registers; it is parked in W.stash[v] = {w, delta | act}.
+__device__ __forceinline__ void stash_put(const psb_darlin_worker& W, int64_t v, const Carry& C, int lane) {
+  if (lane == 0) {
+    __stcg(W.stash + 2 * v, C.act ? C.w : nan_mark());
+    __stcg(W.stash + 2 * v + 1, C.dl);
+  }
+}
+__device__ __forceinline__ void stash_get(const psb_darlin_worker& W, int64_t v, Carry& C) {
+  C.w = __ldcg(W.stash + 2 * v);
+  C.dl = __ldcg(W.stash + 2 * v + 1);
+  C.act = !is_marked(C.w);
 }
 
 template <bool BINARY, bool SINGLE>
@@ -918,56 +854,32 @@ __device__ __forceinline__ double grad_phase_packed(const psb_darlin_worker& W, 
                                                     const ServerHyper& h, const StepPlan& plan,
                                                     int bps, int64_t gw, int64_t nw, int lane,
                                                     const SegRegs& pre, const double* __restrict__ exp_tab,
-                                                    unsigned long long* tp = nullptr, int dbg = 0) {
+                                                    uint32_t tag, Carry& C0) {
   const int64_t total = plan.pref[bps];
   double vio_max = 0;
+  C0.act = false;
   if (gw < total) {
     if (pre.v == gw) {
-      vio_max = grad_segment<BINARY, SINGLE>(W, S, h, pre, lane, exp_tab, tp, dbg);
+      vio_max = grad_segment<BINARY, SINGLE>(W, S, h, pre, lane, exp_tab, tag, C0);
     } else {
       SegRegs R;
-      stage_segment<BINARY>(R, W, plan, bps, gw, lane);
-      vio_max = grad_segment<BINARY, SINGLE>(W, S, h, R, lane, exp_tab, nullptr, dbg);
+      stage_segment<BINARY, SINGLE>(R, W, plan, bps, gw, lane);
+      vio_max = grad_segment<BINARY, SINGLE>(W, S, h, R, lane, exp_tab, tag, C0);
     }
   }
   for (int64_t v = gw + nw; v < total; v += nw) {
     SegRegs R;
-    stage_segment<BINARY>(R, W, plan, bps, v, lane);
-    vio_max = fmax(vio_max, grad_segment<BINARY, SINGLE>(W, S, h, R, lane, exp_tab, nullptr, dbg));
+    Carry C;
+    stage_segment<BINARY, SINGLE>(R, W, plan, bps, v, lane);
+    vio_max = fmax(vio_max, grad_segment<BINARY, SINGLE>(W, S, h, R, lane, exp_tab, tag, C));
+    if (!SINGLE) stash_put(W, v, C, lane);
   }
   return vio_max;
 }
 
-template <bool BINARY, bool MIRROR>
-__device__ __forceinline__ void pull_segment(const psb_darlin_worker& W, const SegRegs& R,
-                                             double delta_max, int lane, uint32_t tag, int tag_dbg = 0) {
-  const uint32_t aw = __ldcg(W.active + (R.j >> 5));
-  if (MIRROR && !(aw >> (R.j & 31) & 1u)) return;  // nothing was pushed, nothing comes back
-  double w_new = 0, d = 0;
-  if (lane == 0) {
-    if (MIRROR) {  // stored here by the owner; the tag of this step makes it valid
-      if (aw >> (R.j & 31) & 1u)
-        mirror_poll(W.mir + 32 * ((int64_t)R.owner * W.mir_cap + R.off), tag, w_new, d);
-    } else {
-      w_new = ld_volatile_f64(W.srv_w[R.owner] + R.off);
-      d = ld_volatile_f64(W.srv_dw[R.owner] + R.off);
-    }
-  }
-  w_new = __shfl_sync(FULL, w_new, 0);
-  d = __shfl_sync(FULL, d, 0);
-  if (is_marked(w_new)) {  // the server filtered this coordinate (ref darlin.h:439-444)
-    if (R.first && lane == 0) {
-      bit_clear_atomic(W.active, R.j);
-      W.w[R.j] = 0;
-    }
-    return;
-  }
-  if (!(aw >> (R.j & 31) & 1u)) return;
-  if (R.first && lane == 0) {
-    W.w[R.j] = w_new;
-    W.delta[R.j] = fmin(delta_max, 2 * fabs(d) + .1);
-  }
-  if (d == 0 || (tag_dbg & 8)) return;
+template <bool BINARY>
+__device__ __forceinline__ void scatter_margins(const psb_darlin_worker& W, const SegRegs& R, double d,
+                                                int lane) {
   uint32_t idx[kUnroll];
   float sv[kUnroll];
 #pragma unroll
@@ -994,74 +906,126 @@ __device__ __forceinline__ void pull_segment(const psb_darlin_worker& W, const S
   }
 }
 
-template <bool BINARY, bool MIRROR>
-__device__ __forceinline__ void pull_phase_packed(const psb_darlin_worker& W, const StepPlan& plan,
-                                                  int bps, double delta_max, int64_t gw, int64_t nw,
-                                                  int lane, const SegRegs& pre, uint32_t tag = 0, int dbg = 0) {
+// Phase 3 of one segment, single rank: the shard was updated in phase 1, read (w, dw) from it.
+template <bool BINARY>
+__device__ __forceinline__ void pull_segment_local(const psb_darlin_worker& W, const SegRegs& R,
+                                                   double delta_max, int lane) {
+  const uint32_t aw = __ldcg(W.active + (R.j >> 5));
+  double w_new = 0, d = 0;
+  if (lane == 0) {
+    w_new = ld_volatile_f64(W.srv_w[R.owner] + R.off);
+    d = ld_volatile_f64(W.srv_dw[R.owner] + R.off);
+  }
+  w_new = __shfl_sync(FULL, w_new, 0);
+  d = __shfl_sync(FULL, d, 0);
+  if (is_marked(w_new)) {  // the server filtered this coordinate (ref darlin.h:439-444)
+    if (R.first && lane == 0) {
+      bit_clear_atomic(W.active, R.j);
+      W.w[R.j] = 0;
+    }
+    return;
+  }
+  if (!(aw >> (R.j & 31) & 1u)) return;
+  if (R.first && lane == 0) {
+    W.w[R.j] = w_new;
+    W.delta[R.j] = fmin(delta_max, 2 * fabs(d) + .1);
+  }
+  if (d == 0) return;
+  scatter_margins<BINARY>(W, R, d, lane);
+}
+
+// Phase 3 of one segment, several ranks: collect the column's (g, u) from the holders' entries in
+// this rank's landing table, apply the update (ref darlin.h:216-245 on the replica, 436-449), and
+// scatter dw into the margins.  The column's first segment writes the replica and, on the owner,
+// the shard.
+template <bool BINARY>
+__device__ __forceinline__ double pull_segment_replica(const psb_darlin_worker& W, const psb_darlin_server& S,
+                                                       const ServerHyper& h, const SegRegs& R,
+                                                       const Carry& C, int lane, uint32_t tag) {
+  const bool mine = R.owner == W.rank;
+  if (!C.act || (R.len == 0 && !mine)) return 0;
+  double gv = 0, uv = 0;
+  if (lane < W.n_workers && (R.has >> lane & 1u))
+    entry_poll(W.land2[W.rank] + entry_index(W, tag, lane, R.j), tag, gv, uv);
+  double g = 0, u = 0;
+  for (int i = 0; i < W.n_workers; ++i) {  // worker order: bit-reproducible, same on every rank
+    g += __shfl_sync(FULL, gv, i);
+    u += __shfl_sync(FULL, uv, i);
+  }
+  const double w = C.w, dl = C.dl;
+  u = u / h.eta + 1e-10;
+  const double g_pos = g + h.lambda, g_neg = g - h.lambda;
+  double d = -w, vio = 0;
+  if (w == 0) {
+    if (g_pos < 0) {
+      vio = -g_pos;
+    } else if (g_neg > 0) {
+      vio = g_neg;
+    } else if (g_pos > h.thr && g_neg < -h.thr) {  // KKT filter: the coordinate leaves the active set
+      if (R.first && lane == 0) {
+        bit_clear_atomic(W.active, R.j);
+        W.w[R.j] = nan_mark();
+        if (mine) {
+          bit_clear_atomic(S.active, R.off);
+          S.w[R.off] = nan_mark();
+          S.dw[R.off] = 0;
+        }
+      }
+      return 0;
+    }
+  }
+  if (g_pos <= u * w) {
+    d = -g_pos / u;
+  } else if (g_neg >= u * w) {
+    d = -g_neg / u;
+  }
+  d = fmin(dl, fmax(-dl, d));
+  const double w_new = w + d;
+  const double dw = w_new - w;
+  if (R.first && lane == 0) {
+    const double dl_new = fmin(h.delta_max, 2 * fabs(d) + .1);
+    W.w[R.j] = w_new;
+    W.delta[R.j] = dl_new;
+    if (mine) {
+      S.w[R.off] = w_new;
+      S.dw[R.off] = dw;
+      S.delta[R.off] = dl_new;
+    }
+  }
+  if (dw != 0) scatter_margins<BINARY>(W, R, dw, lane);
+  return (mine && R.first) ? vio : 0;
+}
+
+template <bool BINARY, bool SINGLE>
+__device__ __forceinline__ double pull_phase_packed(const psb_darlin_worker& W, const psb_darlin_server& S,
+                                                    const ServerHyper& h, const StepPlan& plan, int bps,
+                                                    int64_t gw, int64_t nw, int lane, const SegRegs& pre,
+                                                    uint32_t tag, const Carry& C0) {
   const int64_t total = plan.pref[bps];
+  double vio = 0;
   if (gw < total) {
     if (pre.v == gw) {
-      pull_segment<BINARY, MIRROR>(W, pre, delta_max, lane, tag, dbg);
+      if (SINGLE) pull_segment_local<BINARY>(W, pre, h.delta_max, lane);
+      else vio = pull_segment_replica<BINARY>(W, S, h, pre, C0, lane, tag);
     } else {
       SegRegs R;
-      stage_segment<BINARY>(R, W, plan, bps, gw, lane);
-      pull_segment<BINARY, MIRROR>(W, R, delta_max, lane, tag, dbg);
+      stage_segment<BINARY, SINGLE>(R, W, plan, bps, gw, lane);
+      if (SINGLE) pull_segment_local<BINARY>(W, R, h.delta_max, lane);
+      else vio = pull_segment_replica<BINARY>(W, S, h, R, C0, lane, tag);
     }
   }
   for (int64_t v = gw + nw; v < total; v += nw) {
     SegRegs R;
-    stage_segment<BINARY>(R, W, plan, bps, v, lane);
-    pull_segment<BINARY, MIRROR>(W, R, delta_max, lane, tag, dbg);
+    stage_segment<BINARY, SINGLE>(R, W, plan, bps, v, lane);
+    if (SINGLE) {
+      pull_segment_local<BINARY>(W, R, h.delta_max, lane);
+    } else {
+      Carry C;
+      stash_get(W, v, C);
+      vio = fmax(vio, pull_segment_replica<BINARY>(W, S, h, R, C, lane, tag));
+    }
   }
-}
-
-// same update as server_phase, with every load of a coordinate issued before any use
-__device__ __forceinline__ double server_phase_ilp(const psb_darlin_server& S, const ServerHyper& h,
-                                                   const StepPlan& plan, int bps, int64_t tid,
-                                                   int64_t nthreads) {
-  const int64_t total = plan.pref[bps];
-  double vio_max = 0;
-  for (int64_t v = tid; v < total; v += nthreads) {
-    const int q = locate(plan, bps, v);
-    const int64_t k = plan.first[q] + (v - plan.pref[q]);
-    const uint32_t aw = __ldcg(S.active + (k >> 5));
-    const double w = __ldcg(S.w + k);
-    const double dl = __ldcg(S.delta + k);
-    double g = 0, u = 0;
-    for (int r = 0; r < S.n_workers; ++r) {
-      const int64_t at = (int64_t)r * S.land_cap + k;
-      g += __ldcg(S.land_g + at);
-      u += __ldcg(S.land_u + at);
-    }
-    if (!(aw >> (k & 31) & 1u) || is_marked(w)) continue;
-    u = u / h.eta + 1e-10;
-    const double g_pos = g + h.lambda, g_neg = g - h.lambda;
-    double d = -w, vio = 0;
-    if (w == 0) {
-      if (g_pos < 0) {
-        vio = -g_pos;
-      } else if (g_neg > 0) {
-        vio = g_neg;
-      } else if (g_pos > h.thr && g_neg < -h.thr) {
-        bit_clear_atomic(S.active, k);
-        S.w[k] = nan_mark();
-        S.dw[k] = 0;
-        continue;
-      }
-    }
-    vio_max = fmax(vio_max, vio);
-    if (g_pos <= u * w) {
-      d = -g_pos / u;
-    } else if (g_neg >= u * w) {
-      d = -g_neg / u;
-    }
-    d = fmin(dl, fmax(-dl, d));
-    S.delta[k] = fmin(h.delta_max, 2 * fabs(d) + .1);
-    const double w_new = w + d;
-    S.w[k] = w_new;
-    S.dw[k] = w_new - w;
-  }
-  return vio_max;
+  return vio;
 }
 
 __device__ __forceinline__ void prefetch_l2(const void* p) {
@@ -1096,21 +1060,38 @@ __device__ __forceinline__ void grid_wait_by(const uint32_t* ctr, uint32_t targe
   if (threadIdx.x == leader) spin_gpu_ge(ctr, target);
   __syncthreads();
 }
+// The last barrier of a multi-rank step, plus the flow control of the landing tables: the next
+// step (sequence `next`) may overwrite entries of step next-2, so every peer must have finished
+// that step.  The flags live in this rank's memory and are loaded before the barrier spin, so
+// in the common case (peers at most one step behind) they cost no extra round trip.
+__device__ __forceinline__ void grid_wait_flow(const uint32_t* ctr, uint32_t target,
+                                               const uint64_t* done_local, int n, uint64_t next) {
+  if ((int)threadIdx.x >= kSpinner) {
+    const int lane = threadIdx.x - kSpinner;
+    const bool peer = lane < n;
+    uint64_t seen = peer ? ld_relaxed_sys(done_local + lane) : 0;
+    if (lane == 0) spin_gpu_ge(ctr, target);
+    uint32_t spins = 0;
+    while (peer && seen + 2 < next) {
+      seen = ld_relaxed_sys(done_local + lane);
+      if (++spins > kSpinLimit) __trap();
+    }
+  }
+  __syncthreads();
+}
 
-// bar[0] phase-1 arrivals, bar[1] "server done" step stamp, bar[2] phase-3 arrivals,
-// bar[3] generic barrier (begin / large steps / evaluate).  All zero between launches.
-constexpr int64_t kSingleCtaServerKeys = 16 * kThreads;
-
+// bar[0] phase-1 arrivals, bar[2] phase-3 arrivals, bar[3] generic barrier (begin / evaluate).
+// All zero between launches.
+//
+// `G` CTAs numbered `cta` = 0..G-1 form one rank.  In a real run that is the whole grid; the
+// emulation kernel below runs several ranks side by side in one cooperative launch.
 template <bool BINARY, bool SINGLE>
-__global__ void __launch_bounds__(kThreads, 2)
-k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant__ psb_darlin_server S,
-              const psb_darlin_ctrl* __restrict__ ctrl, const int32_t* __restrict__ order,
-              const int64_t* __restrict__ blk_tab, int n_steps, int bps, uint32_t* bar,
-              psb_darlin_progress* out_local, psb_darlin_progress* const* out_peer, int n_peers,
-              double* scratch, unsigned long long* prof) {
-  __shared__ FusedPlan plans[3];  // steps s, s+1, s+2: built two steps ahead, off the critical path
-  __shared__ double sh[4][kWarps];
-  __shared__ double exp_tab[kExpTab];
+__device__ __forceinline__ void darlin_pass_body(
+    const psb_darlin_worker& W, const psb_darlin_server& S, const psb_darlin_ctrl* __restrict__ ctrl,
+    const int32_t* __restrict__ order, const int64_t* __restrict__ blk_tab, int n_steps, int bps,
+    uint32_t* bar, psb_darlin_progress* out_local, psb_darlin_progress* const* out_peer, int n_peers,
+    double* scratch, unsigned long long* prof, const uint32_t G, const uint32_t cta,
+    FusedPlan* plans, double (*sh)[kWarps], double* exp_tab) {
   fill_exp_table(exp_tab);
   // optional per-phase time accounting (thread 0 of every CTA, summed into prof[0..4])
   unsigned long long t_mark = 0, t_acc[5] = {0, 0, 0, 0, 0};
@@ -1123,20 +1104,17 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
   }
   if (prof && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_mark));
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const uint32_t G = gridDim.x;
   // segment v of a step goes to CTA v % G (warp v / G): a step with fewer segments than warps
   // is spread over every SM instead of filling the first CTAs
-  const int64_t gw = (ctrl->flags & 4) ? (int64_t)blockIdx.x * kWarps + wid : (int64_t)wid * G + blockIdx.x;
+  const int64_t gw = (ctrl->flags & 4) ? (int64_t)cta * kWarps + wid : (int64_t)wid * G + cta;
   const int64_t nw = (int64_t)G * kWarps;
-  const int64_t gt = (int64_t)blockIdx.x * kThreads + threadIdx.x, nt = (int64_t)gridDim.x * kThreads;
+  const int64_t gt = (int64_t)cta * kThreads + threadIdx.x, nt = (int64_t)G * kThreads;
   SegRegs pre;
   pre.v = -1;
   uint32_t nbar = 0;
   const ServerHyper h{ctrl->lambda, ctrl->eta, ctrl->delta_max, ctrl->kkt_threshold};
   const uint64_t seq_base = ctrl->seq_base;
   const bool do_prefetch = !(ctrl->flags & 1);
-  const int dbg = ctrl->flags;  // bits 8 / 16: timing experiments (wrong results), see bench.py
-  const int64_t single_cta_keys = ctrl->server_cta_keys > 0 ? ctrl->server_cta_keys : kSingleCtaServerKeys;
 
   // ---- pass begin (ref darlin.h:176-182, 297-300) ----
   if (gt == 0) *S.violation = 0;
@@ -1149,95 +1127,72 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
       const int64_t rem = S.n_keys - i * 32;
       S.active[i] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
     }
-    if (ctrl->revive_on_reset)
+    if (ctrl->revive_on_reset) {
       for (int64_t i = gt; i < S.n_keys; i += nt)
         if (is_marked(__ldcg(S.w + i))) S.w[i] = 0;
+      if (!SINGLE)
+        for (int64_t i = gt; i < W.n_cols; i += nt)
+          if (is_marked(__ldcg(W.w + i))) W.w[i] = 0;
+    }
   }
   if (wid == 0 && n_steps > 0) fused_plan(plans[0], blk_tab, order, 0, bps);
   if (wid == 1 && n_steps > 1) fused_plan(plans[1], blk_tab, order, 1, bps);
   grid_arrive(bar + 3);
-  if (n_steps > 0 && gw < plans[0].wk.pref[bps]) stage_segment<BINARY>(pre, W, plans[0].wk, bps, gw, lane);
+  if (n_steps > 0 && gw < plans[0].wk.pref[bps]) stage_segment<BINARY, SINGLE>(pre, W, plans[0].wk, bps, gw, lane);
   grid_wait(bar + 3, ++nbar * G);
 
   for (int step = 0; step < n_steps; ++step) {
     const FusedPlan& P = plans[step % 3];
     const FusedPlan& Pn = plans[(step + 1) % 3];
     const uint64_t seq = seq_base + (uint64_t)step + 1;
-    const int64_t nkeys = P.sv.pref[bps];
     const bool has_next = step + 1 < n_steps;
+    Carry C0;
     // ---- phase 1: gradient + push ----
     {
-      unsigned long long* tp = (prof && wid == 0) ? prof + 8 + 2 * (unsigned long long)n_steps + 2 * 4096 + 8 * (blockIdx.x & 7) : nullptr;
-      const double vio = grad_phase_packed<BINARY, SINGLE>(W, S, h, P.wk, bps, gw, nw, lane, pre, exp_tab, tp, dbg);
+      const double vio = grad_phase_packed<BINARY, SINGLE>(W, S, h, P.wk, bps, gw, nw, lane, pre, exp_tab,
+                                                           (uint32_t)seq, C0);
       if (SINGLE && vio > 0) atomic_max_nonneg(S.violation, vio);
     }
     if (prof && threadIdx.x == 0) {  // per-step straggler: max phase-1 time and its CTA
       unsigned long long now_;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
-      atomicMax(prof + 8 + 2 * step, ((now_ - t_mark) << 20) | blockIdx.x);
-      // per-CTA totals behind the per-step records: [sum of phase-1 ns, smid]
-      unsigned smid_;
-      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid_));
-      unsigned long long* per_cta = prof + 8 + 2 * (unsigned long long)n_steps + 2 * blockIdx.x;
-      per_cta[0] += now_ - t_mark;
-      per_cta[1] = smid_;
+      atomicMax(prof + 8 + 2 * step, ((now_ - t_mark) << 20) | cta);
     }
     PSB_PROF(0)
-    if (SINGLE) {
-      // one rank: the shard was updated column by column inside phase 1; a single grid
-      // barrier separates the margin reads of phase 1 from the margin updates of phase 3
-      grid_arrive_by(bar, kSpinner);
-      if (wid == 1 && step + 2 < n_steps) fused_plan(plans[(step + 2) % 3], blk_tab, order, step + 2, bps);
-      if (has_next && do_prefetch && wid != kWarps - 1) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
-      PSB_PROF(1)
-      grid_wait_by(bar, (uint32_t)(step + 1) * G, kSpinner);
-      PSB_PROF(2)
-      pull_phase_packed<BINARY, false>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre, 0, dbg);
-      if (prof && threadIdx.x == 0) {
-        unsigned long long now_;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
-        atomicMax(prof + 9 + 2 * step, ((now_ - t_mark) << 20) | blockIdx.x);
-      }
-      PSB_PROF(3)
-      grid_arrive_by(bar + 2, kSpinner);
-      pre.v = -1;
-      if (has_next && wid != kWarps - 1 && gw < Pn.wk.pref[bps]) stage_segment<BINARY>(pre, W, Pn.wk, bps, gw, lane);
-      grid_wait_by(bar + 2, (uint32_t)(step + 1) * G, kSpinner);
-      PSB_PROF(4)
-      continue;
-    }
-    // ---- more than one rank ----
     // barrier A (local): every margin read of phase 1 precedes every margin update of phase 3.
-    // The pushes are already in flight; the shard update runs between arrive and wait.
+    // Several ranks: the pushes are in flight meanwhile.
     grid_arrive_by(bar, kSpinner);
     if (wid == 1 && step + 2 < n_steps) fused_plan(plans[(step + 2) % 3], blk_tab, order, step + 2, bps);
-    if (nkeys <= single_cta_keys) {
-      // small step: one CTA (the one with the fewest segments) serves the shard
-      if (blockIdx.x == G - 1 && nkeys > 0) {
-        double vio = server_phase_direct(S, h, P.sv, bps, threadIdx.x, kThreads, (uint32_t)seq);
+    if (has_next && do_prefetch && wid != kWarps - 1) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
+    PSB_PROF(1)
+    grid_wait_by(bar, (uint32_t)(step + 1) * G, kSpinner);
+    PSB_PROF(2)
+    // ---- phase 3: (several ranks: collect the entries, update the replica) margins ----
+    {
+      double vio = pull_phase_packed<BINARY, SINGLE>(W, S, h, P.wk, bps, gw, nw, lane, pre, (uint32_t)seq, C0);
+      if (!SINGLE) {
         vio = warp_max(vio);
         if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
       }
-      if (has_next && do_prefetch && wid != kWarps - 1) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
-      PSB_PROF(1)
-      grid_wait_by(bar, (uint32_t)(step + 1) * G, kSpinner);
-    } else {
-      // large step: all CTAs share the coordinates
-      if (has_next && do_prefetch) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
-      double vio = server_phase_direct(S, h, P.sv, bps, gt, nt, (uint32_t)seq);
-      vio = warp_max(vio);
-      if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
-      PSB_PROF(1)
-      grid_wait_by(bar, (uint32_t)(step + 1) * G, kSpinner);
     }
-    // ---- phase 3: every warp polls the mirror entry of its column, then updates margins ----
-    PSB_PROF(2)
-    pull_phase_packed<BINARY, true>(W, P.wk, bps, h.delta_max, gw, nw, lane, pre, (uint32_t)seq, dbg);
+    if (prof && threadIdx.x == 0) {
+      unsigned long long now_;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
+      atomicMax(prof + 9 + 2 * step, ((now_ - t_mark) << 20) | cta);
+    }
     PSB_PROF(3)
     grid_arrive_by(bar + 2, kSpinner);
     pre.v = -1;
-    if (has_next && wid != kWarps - 1 && gw < Pn.wk.pref[bps]) stage_segment<BINARY>(pre, W, Pn.wk, bps, gw, lane);
-    grid_wait_by(bar + 2, (uint32_t)(step + 1) * G, kSpinner);
+    if (has_next && wid != kWarps - 1 && gw < Pn.wk.pref[bps]) stage_segment<BINARY, SINGLE>(pre, W, Pn.wk, bps, gw, lane);
+    if (SINGLE) {
+      grid_wait_by(bar + 2, (uint32_t)(step + 1) * G, kSpinner);
+    } else {
+      grid_wait_flow(bar + 2, (uint32_t)(step + 1) * G, W.done_local, W.n_workers, seq + 1);
+      // this rank has consumed every entry of the step: tell the peers (plain stores, the reads
+      // they guard have returned)
+      if (cta == 0 && (int)threadIdx.x >= kSpinner && (int)threadIdx.x - kSpinner < W.n_workers)
+        *reinterpret_cast<volatile uint64_t*>(W.done_peer[threadIdx.x - kSpinner]) = seq;
+    }
     PSB_PROF(4)
   }
   if (prof && threadIdx.x == 0)
@@ -1261,10 +1216,10 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
   if (threadIdx.x < 4) {
     double a = 0;
     for (int i = 0; i < kWarps; ++i) a += sh[threadIdx.x][i];
-    __stcg(scratch + 4 * (int64_t)blockIdx.x + threadIdx.x, a);
+    __stcg(scratch + 4 * (int64_t)cta + threadIdx.x, a);
   }
   grid_arrive(bar + 3);
-  if (blockIdx.x != 0) return;
+  if (cta != 0) return;
   grid_wait(bar + 3, ++nbar * G);
   double acc[4] = {0, 0, 0, 0};
   for (int b = threadIdx.x; b < (int)G; b += kThreads)
@@ -1295,6 +1250,46 @@ k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant
       if (o) st_release_sys(&o->seq, stamp);
     }
   }
+}
+
+template <bool BINARY, bool SINGLE>
+__global__ void __launch_bounds__(kThreads, 2)
+k_darlin_pass(const __grid_constant__ psb_darlin_worker W, const __grid_constant__ psb_darlin_server S,
+              const psb_darlin_ctrl* __restrict__ ctrl, const int32_t* __restrict__ order,
+              const int64_t* __restrict__ blk_tab, int n_steps, int bps, uint32_t* bar,
+              psb_darlin_progress* out_local, psb_darlin_progress* const* out_peer, int n_peers,
+              double* scratch, unsigned long long* prof) {
+  __shared__ FusedPlan plans[3];  // steps s, s+1, s+2: built two steps ahead, off the critical path
+  __shared__ double sh[4][kWarps];
+  __shared__ double exp_tab[kExpTab];
+  darlin_pass_body<BINARY, SINGLE>(W, S, ctrl, order, blk_tab, n_steps, bps, bar, out_local, out_peer,
+                                   n_peers, scratch, prof, gridDim.x, blockIdx.x, plans, sh, exp_tab);
+}
+
+// Several ranks of the multi-rank pass in ONE cooperative launch on one GPU: CTAs
+// [r*G, (r+1)*G) are rank r.  Kernels of different ranks that wait on each other must not be
+// separate launches on one GPU (nothing guarantees that they run together); here all ranks'
+// CTAs are co-resident by construction, so the single-GPU tests exercise exactly the code of the
+// multi-GPU run: tagged entries, replicated update, flow-control flags.  The "peers" are plain
+// pointers into the same device memory.
+template <bool BINARY>
+__global__ void __launch_bounds__(kThreads, 2)
+k_darlin_pass_emulated(const psb_darlin_rank_args* __restrict__ ranks, int G, int n_steps, int bps,
+                       int n_peers) {
+  __shared__ FusedPlan plans[3];
+  __shared__ double sh[4][kWarps];
+  __shared__ double exp_tab[kExpTab];
+  __shared__ psb_darlin_rank_args A;
+  const int r = blockIdx.x / G;
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(ranks + r);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&A);
+    for (int i = threadIdx.x; i < (int)(sizeof(A) / 4); i += kThreads) dst[i] = src[i];
+  }
+  __syncthreads();
+  darlin_pass_body<BINARY, false>(A.wk, A.sv, A.ctrl, A.order, A.blk_tab, n_steps, bps, A.bar, A.out_local,
+                                  A.out_peer, n_peers, A.scratch, nullptr, (uint32_t)G,
+                                  (uint32_t)(blockIdx.x % G), plans, sh, exp_tab);
 }
 
 }  // namespace psb
@@ -1419,14 +1414,38 @@ PSB_API int psb_darlin_fused_pass(const psb_darlin_worker* wk, const psb_darlin_
                   (void*)&bps, (void*)&bar, (void*)&out_local, (void*)&out_peer, (void*)&np,
                   (void*)&scratch, (void*)&prof};
   const bool single = wk->n_workers == 1 && wk->n_servers == 1;
-  if (!single)
-    PSB_REQUIRE(wk->mir && wk->mir_cap > 0 && sv->has && sv->mir[0],
-                "psb_darlin_fused_pass: the multi-rank pass needs the mirrors and the holder masks "
-                "(worker.mir_*, server.mir_*, server.has) and EMPTY-filled landing slots");
+  if (!single) {
+    PSB_REQUIRE(wk->n_workers <= PSB_MAX_PEERS && wk->n_workers <= 32, "psb_darlin_fused_pass: too many ranks");
+    PSB_REQUIRE(wk->col_has && wk->stash && wk->done_local && wk->land2[wk->rank],
+                "psb_darlin_fused_pass: the multi-rank pass needs the landing tables, the holder masks, "
+                "the stash and the flow-control flags (worker.land2, col_has, stash, done_*)");
+  }
   const void* fn = wk->sval
       ? (single ? (const void*)k_darlin_pass<false, true> : (const void*)k_darlin_pass<false, false>)
       : (single ? (const void*)k_darlin_pass<true, true> : (const void*)k_darlin_pass<true, false>);
   PSB_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), args, 0, (cudaStream_t)stream));
+  return 0;
+}
+
+// Emulation of `n_ranks` ranks of the multi-rank pass on ONE GPU in one cooperative launch (see
+// k_darlin_pass_emulated).  `ranks_dev`: device array of n_ranks argument records whose peer
+// pointers point into the same device; grid_per_rank * n_ranks must not exceed
+// psb_darlin_fused_max_grid().
+PSB_API int psb_darlin_fused_pass_emulated(const psb_darlin_rank_args* ranks_dev, int32_t n_ranks,
+                                           int32_t binary, int32_t n_steps, int32_t bps,
+                                           int32_t grid_per_rank, int32_t n_peers, void* stream) {
+  PSB_REQUIRE(ranks_dev && n_ranks >= 2 && n_ranks <= PSB_MAX_PEERS, "psb_darlin_fused_pass_emulated: bad ranks");
+  if (int rc = check_step_args("psb_darlin_fused_pass_emulated", bps, grid_per_rank)) return rc;
+  int per_sm = 0;
+  PSB_CUDA(binary ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_darlin_pass_emulated<true>, kThreads, 0)
+                  : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_darlin_pass_emulated<false>, kThreads, 0));
+  PSB_REQUIRE((int64_t)grid_per_rank * n_ranks <= (int64_t)per_sm * sm_count(),
+              "psb_darlin_fused_pass_emulated: %d x %d CTAs exceed the co-resident maximum %d",
+              n_ranks, grid_per_rank, per_sm * sm_count());
+  void* args[] = {(void*)&ranks_dev, (void*)&grid_per_rank, (void*)&n_steps, (void*)&bps, (void*)&n_peers};
+  const void* fn = binary ? (const void*)k_darlin_pass_emulated<true> : (const void*)k_darlin_pass_emulated<false>;
+  PSB_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid_per_rank * n_ranks), dim3(kThreads), args, 0,
+                                       (cudaStream_t)stream));
   return 0;
 }
 

@@ -227,11 +227,17 @@ class TcpVan : public Van {
     std::vector<uint64> lens;
     for (auto& f : frames) lens.push_back(f.second);
     uint32 pre[2] = {WireCodec::kMagic, (uint32)frames.size()};
-    if (!writeAll(p->fd, pre, sizeof(pre)) || !writeAll(p->fd, lens.data(), lens.size() * 8))
+    // a partial write leaves the byte stream out of frame: drop the connection, the next
+    // message reconnects
+    auto fail = [&] {
+      ::close(p->fd);
+      p->fd = -1;
       return Status::IOError("send to " + msg->recver + " failed");
+    };
+    if (!writeAll(p->fd, pre, sizeof(pre)) || !writeAll(p->fd, lens.data(), lens.size() * 8))
+      return fail();
     for (auto& f : frames)
-      if (f.second && !writeAll(p->fd, f.first, f.second))
-        return Status::IOError("send to " + msg->recver + " failed");
+      if (f.second && !writeAll(p->fd, f.first, f.second)) return fail();
     if (send_bytes) *send_bytes = total;
     countSend(p->host == "127.0.0.1" ? my_host_ : p->host, total);
     logMsg("SND", *msg);
@@ -355,23 +361,36 @@ class TcpVan : public Van {
         break;
       std::vector<uint64> lens(pre[1]);
       if (!readAll(fd, lens.data(), lens.size() * 8)) break;
-      string head(lens[0], 0);
-      if (!readAll(fd, &head[0], head.size())) break;
-      MessagePtr m;
-      if (!WireCodec::parseHead(head, &m)) break;
-      m->recver = my_id_;
-      size_t total = head.size(), i = 1;
+      // the listener accepts anything that can reach the port: never trust the lengths
+      bool sane = lens[0] <= kMaxHeadBytes;
+      for (size_t k = 1; sane && k < lens.size(); ++k) sane = lens[k] <= kMaxFrameBytes;
+      if (!sane) break;
       bool ok = true;
-      if (m->task.has_key() && i < lens.size()) {
-        m->key.resize(lens[i]);
-        ok = lens[i] == 0 || readAll(fd, m->key.data(), lens[i]);
-        total += lens[i++];
-      }
-      for (; ok && i < lens.size(); ++i) {
-        SArray<char> v(lens[i]);
-        ok = lens[i] == 0 || readAll(fd, v.data(), lens[i]);
-        m->value.push_back(v);
-        total += lens[i];
+      size_t total = 0;
+      MessagePtr m;
+      try {
+        string head(lens[0], 0);
+        if (!readAll(fd, &head[0], head.size())) break;
+        if (!WireCodec::parseHead(head, &m)) break;
+        m->recver = my_id_;
+        size_t i = 1;
+        total = head.size();
+        // the header says how many frames follow: a key frame (if any) and one per value type
+        const size_t want = (m->task.has_key() ? 1 : 0) + m->task.value_type_size();
+        if (m->task.value_type_size() > 0 && lens.size() - 1 != want) break;
+        if (m->task.has_key() && i < lens.size()) {
+          m->key.resize(lens[i]);
+          ok = lens[i] == 0 || readAll(fd, m->key.data(), lens[i]);
+          total += lens[i++];
+        }
+        for (; ok && i < lens.size(); ++i) {
+          SArray<char> v(lens[i]);
+          ok = lens[i] == 0 || readAll(fd, v.data(), lens[i]);
+          m->value.push_back(v);
+          total += lens[i];
+        }
+      } catch (const std::exception&) {  // bad_alloc / length_error on a hostile frame
+        break;
       }
       if (!ok) break;
       countRecv(host == "127.0.0.1" ? my_host_ : host, total);
@@ -380,6 +399,8 @@ class TcpVan : public Van {
     ::close(fd);
   }
 
+  static constexpr uint64 kMaxHeadBytes = 64ull << 20;   // text header incl. app configs
+  static constexpr uint64 kMaxFrameBytes = 1ull << 36;   // 64 GiB per data frame
   int listen_fd_ = -1;
   std::atomic<bool> closing_{false};
   std::thread accept_thread_;

@@ -41,14 +41,10 @@ typedef struct psb_darlin_ctrl {
   int32_t n_steps;           /* steps in this pass */
   int32_t revive_on_reset;   /* 1: a reset also un-marks filtered weights (w=NaN -> 0); the
                                 reference leaves them NaN forever, default 0 */
-  int32_t server_cta_keys;   /* persistent kernel: steps with at most this many shard keys are
-                                updated by one CTA (0 = default 4096); larger ones by the grid */
+  int32_t reserved0;
   int32_t flags;             /* persistent pass kernel only.  1: do not prefetch the next step's CSC
                               * ranges into L2; 4: fill CTAs one after the other with segments instead
-                              * of dealing segments round robin over all CTAs.  8, 16, 32 are timing
-                              * experiments that produce WRONG results (skip the margin updates / the
-                              * margin gather + arithmetic / the arithmetic only), see
-                              * profiles/README.md "Where a step goes". */
+                              * of dealing segments round robin over all CTAs. */
   int32_t reserved;
 } psb_darlin_ctrl;
 
@@ -95,10 +91,16 @@ typedef struct psb_darlin_worker {
   const uint64_t* ver_flag;           /* local: [n_servers], written by the servers */
   const void* seg_meta;               /* [n_seg] int4 {col, len | first<<16 | single<<17, beg lo,
                                          beg hi}: one 16-byte load per segment (fused kernel) */
-  /* fused multi-rank pass: the owners store every updated coordinate into this worker's own
-   * mirror (32-byte tagged entries, index owner*mir_cap + col_off), so the pull is local */
-  const char* mir;
-  int64_t mir_cap;
+  /* fused multi-rank pass (replicated update, see darlin.cu): land2[q] = rank q's landing table
+   * of 32-byte tagged entries [2 parities][n_workers][n_cols]; col_has[j] bit r = worker r holds
+   * nonzeros of column j; stash = [2*max segments per step] phase-1 state parked for phase 3;
+   * done_local[q] = last step rank q finished (written by q), done_peer[q] = &done_local of rank
+   * q at index `rank` */
+  char* land2[PSB_MAX_PEERS];
+  const uint32_t* col_has;
+  double* stash;
+  const uint64_t* done_local;
+  uint64_t* done_peer[PSB_MAX_PEERS];
 } psb_darlin_worker;
 
 /* Server side: one key-range shard of the model. */
@@ -117,15 +119,7 @@ typedef struct psb_darlin_server {
   int64_t n_keys;
   int32_t rank, n_workers, n_servers;
   uint64_t* ver_flag[PSB_MAX_PEERS];  /* on worker r: &ver_flag_r[rank] */
-  /* fused multi-rank pass */
-  char* mir[PSB_MAX_PEERS];           /* on worker r: &mir_r[32*rank*mir_cap] */
-  const uint32_t* has;                /* [n_keys] bit r set: worker r holds nonzeros of the key */
 } psb_darlin_server;
-
-/* Bit pattern of an empty landing slot in the fused multi-rank pass (a quiet NaN that no
- * arithmetic produces).  A worker's push overwrites it; the server polls for "not empty",
- * consumes the value and stores the pattern back: the data is its own arrival flag. */
-#define PSB_DARLIN_EMPTY_SLOT 0x7ff8dead5107e001ull
 
 /* Pass begin: violation=0 and, if ctrl->reset_kkt_filter, refill the active sets.
  * Either struct pointer may be NULL. ref: darlin.h:176-182,297-300 */
@@ -182,6 +176,8 @@ int psb_darlin_enqueue_pass(const psb_darlin_worker* wk, const psb_darlin_server
  *     every GPU loading the library holds until exit); larger grids are rejected with an error;
  *   - the first call on a device looks up the array's device address (one-time set-up with that
  *     device current); make that first call before starting any stream capture;
+ *   - the array is chosen by the CURRENT device (cudaGetDevice), so the current device must be
+ *     the one `stream` belongs to; otherwise the kernel would be handed another GPU's array;
  *   - all calls on a device share the one array: calls that overlap on the GPU (different
  *     streams) race on it, so serialise them; nothing is written to peers (out_local only). */
 int32_t psb_darlin_evaluate_noalloc_max_grid(void);
@@ -195,6 +191,12 @@ int psb_darlin_evaluate_noalloc(const psb_darlin_worker* wk, const psb_darlin_se
  * owned by the caller.  blk_tab[b] = {first segment, #segments, first shard key, #shard keys,
  * server mask, 0}.  grid <= psb_darlin_fused_max_grid().  prof (optional): 5 uint64 that
  * accumulate ns spent in {phase 1, plan+prefetch, barrier A wait, phase 3, barrier C}. */
+/* Several ranks: every rank keeps a replica of (w, delta, active) for all columns; a push is one
+ * tagged entry per column stored into the landing table of every rank that holds or owns the
+ * column (one NVLink flight per step), phase 3 sums the holders' entries in worker order and
+ * applies the update on every rank identically; the owner also writes its shard.  Needs
+ * worker.land2 / col_has / stash / done_local / done_peer; worker.w must start as a copy of the
+ * shard weights. */
 int psb_darlin_fused_max_grid(int32_t binary);
 int psb_darlin_fused_pass(const psb_darlin_worker* wk, const psb_darlin_server* sv,
                           const psb_darlin_ctrl* ctrl, const int32_t* order,
@@ -203,6 +205,25 @@ int psb_darlin_fused_pass(const psb_darlin_worker* wk, const psb_darlin_server* 
                           psb_darlin_progress* const* out_peer, int32_t n_peers, double* scratch,
                           uint64_t* prof, void* stream);
 
+
+/* The multi-rank pass of `n_ranks` ranks emulated on ONE GPU in one cooperative launch (CTAs
+ * [r*grid_per_rank, (r+1)*grid_per_rank) are rank r; peers are pointers into the same device).
+ * Ranks that wait on each other must not be separate launches on one GPU; this entry lets a
+ * single-GPU box run the exact multi-GPU code path.  ranks_dev: device array of n_ranks records. */
+typedef struct psb_darlin_rank_args {
+  psb_darlin_worker wk;
+  psb_darlin_server sv;
+  const psb_darlin_ctrl* ctrl;
+  const int32_t* order;
+  const int64_t* blk_tab;
+  uint32_t* bar;
+  psb_darlin_progress* out_local;
+  psb_darlin_progress* const* out_peer;
+  double* scratch;
+} psb_darlin_rank_args;
+int psb_darlin_fused_pass_emulated(const psb_darlin_rank_args* ranks_dev, int32_t n_ranks,
+                                   int32_t binary, int32_t n_steps, int32_t blocks_per_step,
+                                   int32_t grid_per_rank, int32_t n_peers, void* stream);
 
 /* ------------------------------------------------------------------------- *
  *  Asynchronous minibatch SGD (FTRL / AdaGrad / SGD) on a sharded hash store

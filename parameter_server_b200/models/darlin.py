@@ -61,8 +61,10 @@ class DarlinConfig:
     seed: int = 0
     use_graph: bool = True
     fused: bool = True                # one persistent cooperative kernel per pass
-    server_cta_keys: int = 0          # 0 = kernel default (see psb_darlin_ctrl)
     kernel_flags: int = 0             # psb_darlin_ctrl.flags
+    collectives: str = "peer"         # "peer": kernels store / load peer memory directly;
+    #                                   "nccl": the comparison variant (split kernels with
+    #                                   all_to_all + all_gather between them, models/darlin_nccl.py)
     fused_grid: int = 0               # 0 = all co-resident CTAs
     profile_phases: bool = False      # accumulate per-phase %globaltimer time (debug)
 
@@ -314,15 +316,18 @@ class DarlinEngine:
         cap = max(max(self.shard_len), 1)
         self.land_cap = cap
         self.bps = max(1, min(cfg.max_block_delay + 1, 32))
-        nbytes = (2 * W * cap + 2 * cap + 4 * W * cap) * 8 + (2 * W + 4 * W) * 8 + W * 48 + 64 * 256
+        ncols = max(self.n_cols, 1)
+        nbytes = (2 * W * cap + 2 * cap) * 8 + 2 * W * ncols * 32 + 8 * W * 8 + W * 48 + 64 * 256
         self.arena = self.comm.make_arena(nbytes, dev)
         A = self.arena
         self.b_land_g = A.alloc("land_g", W * cap, torch.float64)
         self.b_land_u = A.alloc("land_u", W * cap, torch.float64)
         self.b_w = A.alloc("w", cap, torch.float64)
         self.b_dw = A.alloc("dw", cap, torch.float64)
-        # fused multi-rank pass: mirrors of every shard, written by the owners (psb200.h)
-        self.b_mir = A.alloc("mirror", 4 * W * cap, torch.float64)  # 32-byte tagged entries
+        # fused multi-rank pass: tagged (g, u) entries [2 parities][W workers][n_cols], written by
+        # the workers of every rank (psb200.h), and the flow-control flags
+        self.b_land2 = A.alloc("land2", 2 * W * ncols * 4, torch.float64)
+        self.b_done = A.alloc("done", W, torch.int64)
         self.b_push_flag = A.alloc("push_flag", W, torch.int64)
         self.b_ver_flag = A.alloc("ver_flag", W, torch.int64)
         self.b_bar_flag = A.alloc("bar_flag", W, torch.int64)
@@ -338,6 +343,7 @@ class DarlinEngine:
         self.wk_delta = torch.full((max(self.n_cols, 1),), cfg.delta_init_value, **f64)
         self.wk_active = _full_bitmap(self.n_cols, dev)
         self.part = torch.zeros(2 * self.bps * max(self.max_blk_segs, 1), **f64)
+        self.stash = torch.zeros(2 * self.bps * max(self.max_blk_segs, 1), **f64)
         self.col_cnt = torch.zeros(max(self.n_cols, 1), dtype=torch.int32, device=dev)
         self.ctrs = torch.zeros(16, dtype=torch.int32, device=dev)
         sm = torch.cuda.get_device_properties(dev).multi_processor_count
@@ -348,11 +354,11 @@ class DarlinEngine:
         if cfg.fused_grid > 0:
             self.grid_fused = min(self.grid_fused, cfg.fused_grid)
         self.bar = torch.zeros(4, dtype=torch.int32, device=dev)
-        self.prof = torch.zeros(8 + 2 * (len(self.blocks) + len(self.prior_blk_order) + 2) + 2 * 4096 + 64, dtype=torch.int64, device=dev)
+        self.prof = torch.zeros(8 + 4 * (len(self.blocks) + len(self.prior_blk_order) + 8) + 64, dtype=torch.int64, device=dev)
         self.eval_scratch = torch.zeros(
             K.evaluate_scratch_bytes(max(self.grid_eval, 4 * sm)) // 8 + 2, **f64)
         # host-pinned staging for the per-pass inputs / result
-        max_steps = len(self.blocks) + len(self.prior_blk_order) + 1
+        max_steps = 2 * (len(self.blocks) + len(self.prior_blk_order)) + 8  # room for repeated blocks
         self.order_host = torch.full((max_steps * self.bps,), -1, dtype=torch.int32).pin_memory()
         self.order_dev = torch.full((max_steps * self.bps,), -1, dtype=torch.int32, device=dev)
         self.ctrl_host = torch.zeros(C.sizeof(K.DarlinCtrl), dtype=torch.uint8).pin_memory()
@@ -382,7 +388,12 @@ class DarlinEngine:
             wk.srv_dw[s] = A.peer_ptr(s, self.b_dw)
         wk.ver_flag = self.b_ver_flag.ptr
         wk.seg_meta = self.seg_meta.data_ptr()
-        wk.mir, wk.mir_cap = self.b_mir.ptr, cap
+        self.col_has = self._column_holders()
+        wk.col_has, wk.stash = self.col_has.data_ptr(), self.stash.data_ptr()
+        wk.done_local = self.b_done.ptr
+        for s in range(W):
+            wk.land2[s] = A.peer_ptr(s, self.b_land2)
+            wk.done_peer[s] = A.peer_ptr(s, self.b_done, self.rank)
         self.wk = wk
 
         sv = K.DarlinServer()
@@ -394,14 +405,10 @@ class DarlinEngine:
         sv.n_keys, sv.rank, sv.n_workers, sv.n_servers = n_keys, self.rank, W, W
         for r in range(W):
             sv.ver_flag[r] = A.peer_ptr(r, self.b_ver_flag, self.rank)
-            sv.mir[r] = A.peer_ptr(r, self.b_mir, 4 * self.rank * cap)
-        self.srv_has = self._holder_masks()
-        sv.has = self.srv_has.data_ptr()
-        self.direct_landing = bool(cfg.fused and W > 1 and self.grid_fused > 0)
-        if self.direct_landing:  # slots are their own arrival flags (PSB_DARLIN_EMPTY_SLOT)
-            empty = torch.tensor([K.EMPTY_SLOT], dtype=torch.int64, device=dev)
-            self.b_land_g.tensor.view(torch.int64).copy_(empty.expand(W * cap))
-            self.b_land_u.tensor.view(torch.int64).copy_(empty.expand(W * cap))
+        # the replicated multi-rank pass and the split kernels keep the workers' copies of the
+        # filter marks differently: an engine runs one or the other
+        self.replicated = bool(cfg.fused and W > 1 and self.grid_fused > 0)
+        self._passes_run = 0
         self.sv = sv
         self.prog_peer = torch.tensor([A.peer_ptr(r, self.b_progress, 6 * self.rank)
                                        for r in range(W)], dtype=torch.int64, device=dev)
@@ -410,21 +417,13 @@ class DarlinEngine:
         torch.cuda.synchronize(dev)
         self.comm.barrier()
 
-    def _holder_masks(self) -> torch.Tensor:
-        """has[k] bit r: worker r holds nonzeros of shard key k (it pushes that key every time
-        the key is active).  Set-up time exchange: one byte per (worker, column)."""
-        dev, W = self.device, self.world
+    def _column_holders(self) -> torch.Tensor:
+        """col_has[j] bit r: worker r holds nonzeros of column j (it pushes the column whenever
+        the column is active).  Set-up time exchange: one byte per (worker, column)."""
         present = (self.col_ptr[1:] > self.col_ptr[:-1]).to(torch.uint8)
-        parts = []
-        for s in range(W):
-            cols = (self.col_owner == s).nonzero().flatten()
-            dense = torch.zeros(self.shard_len[s], dtype=torch.uint8, device=dev)
-            dense[self.col_off[cols]] = present[cols]
-            parts.append(dense)
-        got = self.comm.alltoall_var(parts)
-        has = torch.zeros(max(self.shard_len[self.rank], 1), dtype=torch.int32, device=dev)
-        for r in range(W):
-            has[:got[r].numel()] |= got[r].to(torch.int32) << r
+        has = torch.zeros(max(self.n_cols, 1), dtype=torch.int32, device=self.device)
+        for r, p in enumerate(self.comm.gather_var(present)):
+            has[:p.numel()] |= p.to(self.device).to(torch.int32) << r
         return has
 
     def _warm_kernels(self) -> None:
@@ -444,18 +443,16 @@ class DarlinEngine:
     # one pass
     # ----------------------------------------------------------------------------------------
     def use_split_protocol(self) -> None:
-        """Switch the landing slots to the flag protocol of the split kernels (zero-filled,
-        push flags).  Used by the lock-step emulation, which cannot run the persistent kernel
-        of several ranks on one GPU."""
-        if self.direct_landing:
-            self.b_land_g.tensor.zero_()
-            self.b_land_u.tensor.zero_()
-            self.direct_landing = False
+        """Run this engine with the split kernels (landing slots + push / version flags) instead
+        of the persistent multi-rank pass.  Only before the first pass: the two keep the
+        workers' copies of the KKT-filter marks differently."""
+        if self.replicated:
+            if self._passes_run:
+                raise RuntimeError("cannot switch protocols after a pass has run")
+            self.replicated = False
 
     def _enqueue(self, n_steps: int) -> None:
-        if self.cfg.fused and self.grid_fused > 0:
-            if self.world > 1 and not self.direct_landing:
-                raise RuntimeError("this engine was switched to the split-kernel landing protocol")
+        if self.cfg.fused and self.grid_fused > 0 and (self.world == 1 or self.replicated):
             K.fused_pass(self.wk, self.sv, self.ctrl_dev.data_ptr(), self.order_dev.data_ptr(),
                          self.blk_tab.data_ptr(), n_steps, self.bps, self.grid_fused,
                          self.bar.data_ptr(),
@@ -497,7 +494,7 @@ class DarlinEngine:
         self.order_host[:flat.size] = torch.from_numpy(flat)
         ctrl = K.DarlinCtrl(kkt_threshold, cfg.lambda_l1, cfg.eta, cfg.delta_max_value, self._seq,
                             int(reset_kkt_filter), n_steps, int(cfg.revive_on_reset),
-                            int(cfg.server_cta_keys), int(cfg.kernel_flags), 0)
+                            0, int(cfg.kernel_flags), 0)
         self.ctrl_host.copy_(torch.frombuffer(bytearray(bytes(ctrl)), dtype=torch.uint8))
         self.order_dev[:flat.size].copy_(self.order_host[:flat.size], non_blocking=True)
         self.ctrl_dev.copy_(self.ctrl_host, non_blocking=True)
@@ -509,7 +506,8 @@ class DarlinEngine:
         """Merge the progress records of all ranks (already copied to pinned host memory)."""
         self._seq += n_steps
         self._pass_index += 1
-        fused = self.cfg.fused and self.grid_fused > 0
+        self._passes_run += 1
+        fused = self.cfg.fused and self.grid_fused > 0 and (self.world == 1 or self.replicated)
         self.launches_per_pass = (1 if fused else 2 + 3 * n_steps) + (1 if self.world > 1 else 0)
         self.d2h_bytes_per_pass = self.prog_host.numel() * 8
         p = Progress()
@@ -551,6 +549,72 @@ class DarlinEngine:
         p.device_ms = ev[0].elapsed_time(ev[3])
         p.kernel_ms = ev[1].elapsed_time(ev[2])
         return p
+
+    def capture(self, n_steps: int | None = None) -> None:
+        """Capture the pass graph ahead of the first pass (set-up, changes no state)."""
+        if not self.cfg.use_graph:
+            return
+        n_steps = n_steps if n_steps is not None else len(self.plan_steps(list(self.blk_order)))
+        if n_steps in self._graphs:
+            return
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=self._side_stream()):
+            self._enqueue(n_steps)
+        self._graphs[n_steps] = g
+
+    def reset_model(self) -> None:
+        """Back to the zero model (init_w = ZERO): weights, margins, trust regions, active sets."""
+        torch.cuda.synchronize(self.device)
+        self.comm.barrier()
+        self.b_w.tensor.zero_(); self.b_dw.tensor.zero_()
+        self.b_land_g.tensor.zero_(); self.b_land_u.tensor.zero_()
+        self.z.zero_(); self.w_cache.zero_(); self.violation.zero_()
+        self.srv_delta.fill_(self.cfg.delta_init_value)
+        self.wk_delta.fill_(self.cfg.delta_init_value)
+        self.srv_active.copy_(_full_bitmap(self.n_keys, self.device))
+        self.wk_active.copy_(_full_bitmap(self.n_cols, self.device))
+        self.progress = []
+        self._order_rng = np.random.RandomState(self.cfg.seed + 23)
+        torch.cuda.synchronize(self.device)
+        self.comm.barrier()
+
+    def gather_weights(self) -> torch.Tensor:
+        """The whole model in local-column order (= concatenated group dictionaries), assembled
+        from every rank's shard; KKT-filtered (NaN-marked) weights read as 0."""
+        parts = self.comm.gather_var(self.shard_weights().clone())
+        w = torch.zeros(max(self.n_cols, 1), dtype=torch.float64, device=self.device)
+        for s, ws in enumerate(parts):
+            ws = ws.to(self.device)
+            for gid in self.grp_ids:
+                lo, hi = self.slices[gid][s]
+                base, cb = self.shard_base[(gid, s)], self.col_base[gid]
+                w[cb + lo:cb + hi] = ws[base:base + hi - lo]
+        return torch.nan_to_num(w, nan=0.0)
+
+    def verify(self, reported_objective: float | None = None, tol: float = 1e-9) -> dict:
+        """Invariant check with plain fp64 torch (outside any timed region): the margins the
+        kernels maintain incrementally must equal y_i <x_i, w> recomputed from the gathered
+        shards, and the objective recomputed from them must equal the reported one."""
+        w = self.gather_weights()
+        counts = self.col_ptr[1:] - self.col_ptr[:-1]
+        col = torch.repeat_interleave(torch.arange(self.n_cols, device=self.device), counts)
+        rows = self.row_idx.long()
+        sv = self.sval.double() if self.sval is not None else self.y.double()[rows]
+        z_ref = torch.zeros_like(self.z).index_add_(0, rows, sv * w[col])
+        del col, sv
+        err = ((z_ref - self.z).abs() / (1 + z_ref.abs())).max().item() if self.n_rows else 0.0
+        loss = torch.where(z_ref > 0, torch.log1p(torch.exp(-z_ref)),
+                           -z_ref + torch.log1p(torch.exp(z_ref))).sum().item()
+        pen = self.cfg.lambda_l1 * self.shard_weights().nan_to_num(nan=0.0).abs().sum().item()
+        obj = self.comm.allreduce_sum([loss + pen], self.device)[0]
+        errs = self.comm.gather_obj(err)
+        out = {"max_rel_margin_error": max(errs), "objective_recomputed": obj}
+        ok = max(errs) <= tol
+        if reported_objective is not None:
+            out["objective_rel_error"] = abs(obj - reported_objective) / max(abs(obj), 1e-300)
+            ok = ok and out["objective_rel_error"] <= tol
+        out["verified"] = bool(ok)
+        return out
 
     def _side_stream(self):
         if not hasattr(self, "_cap_stream"):
@@ -668,6 +732,37 @@ def run_pass_lockstep(engines: list, order: list, kkt_threshold: float, reset: b
         K.evaluate(e.wk, e.sv, e.ctrl_dev.data_ptr(),
                    e.arena.peer_ptr(e.rank, e.b_progress, 6 * e.rank), e.prog_peer.data_ptr(),
                    e.world, 0, e.eval_scratch.data_ptr(), e.grid_eval)
+    torch.cuda.synchronize()
+    out = None
+    for e in engines:
+        e.prog_host.copy_(e.b_progress.tensor)
+        p = e.finish_pass(n_steps)
+        out = out or p
+    return out
+
+
+def run_pass_emulated(engines: list, order: list, kkt_threshold: float, reset: bool,
+                      n_prior: int = 0, grid_per_rank: int = 0) -> Progress:
+    """All ranks of the persistent multi-rank pass in ONE cooperative launch on one GPU
+    (psb_darlin_fused_pass_emulated): the engines live in one process (ThreadComm), their
+    "peers" are pointers into the same device.  Exercises exactly the multi-GPU code path."""
+    e0 = engines[0]
+    R = len(engines)
+    assert all(e.replicated for e in engines), "engines were switched to the split protocol"
+    n_steps = 0
+    for e in engines:
+        n_steps = e.stage_pass(order, kkt_threshold, reset, n_prior)
+    if grid_per_rank <= 0:
+        grid_per_rank = max(1, min(e0.grid_fused // R, 64))
+    recs = (K.DarlinRankArgs * R)()
+    for r, e in enumerate(engines):
+        recs[r].wk, recs[r].sv = e.wk, e.sv
+        recs[r].ctrl, recs[r].order = e.ctrl_dev.data_ptr(), e.order_dev.data_ptr()
+        recs[r].blk_tab, recs[r].bar = e.blk_tab.data_ptr(), e.bar.data_ptr()
+        recs[r].out_local = e.arena.peer_ptr(e.rank, e.b_progress, 6 * e.rank)
+        recs[r].out_peer, recs[r].scratch = e.prog_peer.data_ptr(), e.eval_scratch.data_ptr()
+    raw = torch.frombuffer(bytearray(bytes(recs)), dtype=torch.uint8).to(e0.device)
+    K.fused_pass_emulated(raw.data_ptr(), R, e0.sval is None, n_steps, e0.bps, grid_per_rank, R)
     torch.cuda.synchronize()
     out = None
     for e in engines:

@@ -38,7 +38,7 @@ CUDA_SIGS = {
     "psb_darlin_pass_begin": "pppp", "psb_darlin_grad_push": "pppiiip",
     "psb_darlin_server_update": "pppiiip", "psb_darlin_pull_update": "pppiiip",
     "psb_darlin_evaluate": "pppppiQpip", "psb_darlin_fused_pass": "pppppiiipppippp",
-    "psb_darlin_fused_max_grid": "i", "psb_darlin_enqueue_pass": "ppppiiiippipip",
+    "psb_darlin_fused_max_grid": "i", "psb_darlin_fused_pass_emulated": "piiiiiip", "psb_darlin_enqueue_pass": "ppppiiiippipip",
 }
 _applied = False
 

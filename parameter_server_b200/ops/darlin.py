@@ -14,7 +14,7 @@ class DarlinCtrl(C.Structure):
     _fields_ = [("kkt_threshold", C.c_double), ("lambda_", C.c_double), ("eta", C.c_double),
                 ("delta_max", C.c_double), ("seq_base", C.c_uint64),
                 ("reset_kkt_filter", C.c_int32), ("n_steps", C.c_int32),
-                ("revive_on_reset", C.c_int32), ("server_cta_keys", C.c_int32),
+                ("revive_on_reset", C.c_int32), ("reserved0", C.c_int32),
                 ("flags", C.c_int32), ("reserved", C.c_int32)]
 
 
@@ -33,7 +33,8 @@ class DarlinWorker(C.Structure):
                 ("land_g", P * MAX_PEERS), ("land_u", P * MAX_PEERS),
                 ("land_cap", C.c_int64 * MAX_PEERS), ("push_flag", P * MAX_PEERS),
                 ("srv_w", P * MAX_PEERS), ("srv_dw", P * MAX_PEERS), ("ver_flag", P),
-                ("seg_meta", P), ("mir", P), ("mir_cap", C.c_int64)]
+                ("seg_meta", P), ("land2", P * MAX_PEERS), ("col_has", P), ("stash", P),
+                ("done_local", P), ("done_peer", P * MAX_PEERS)]
 
 
 class DarlinServer(C.Structure):
@@ -41,10 +42,13 @@ class DarlinServer(C.Structure):
                 ("land_cap", C.c_int64), ("push_flag", P), ("blk_rng", P), ("violation", P),
                 ("done_ctr", P), ("n_keys", C.c_int64), ("rank", C.c_int32),
                 ("n_workers", C.c_int32), ("n_servers", C.c_int32),
-                ("ver_flag", P * MAX_PEERS), ("mir", P * MAX_PEERS),
-                ("has", P)]
+                ("ver_flag", P * MAX_PEERS)]
 
-EMPTY_SLOT = 0x7ff8dead5107e001  # include/psb200.h PSB_DARLIN_EMPTY_SLOT
+
+class DarlinRankArgs(C.Structure):
+    """psb_darlin_rank_args: one rank of the single-GPU emulation of the multi-rank pass."""
+    _fields_ = [("wk", DarlinWorker), ("sv", DarlinServer), ("ctrl", P), ("order", P),
+                ("blk_tab", P), ("bar", P), ("out_local", P), ("out_peer", P), ("scratch", P)]
 
 
 def _lib():
@@ -103,3 +107,9 @@ def fused_pass(wk, sv, ctrl_ptr: int, order_ptr: int, blk_tab_ptr: int, n_steps:
     check(_lib().psb_darlin_fused_pass(_ref(wk), _ref(sv), ctrl_ptr, order_ptr, blk_tab_ptr,
                                        n_steps, bps, grid, bar_ptr, out_local, out_peer, n_peers,
                                        scratch_ptr, prof_ptr, current_stream()))
+
+
+def fused_pass_emulated(ranks_dev_ptr: int, n_ranks: int, binary: bool, n_steps: int, bps: int,
+                        grid_per_rank: int, n_peers: int):
+    check(_lib().psb_darlin_fused_pass_emulated(ranks_dev_ptr, n_ranks, int(binary), n_steps, bps,
+                                                grid_per_rank, n_peers, current_stream()))

@@ -28,15 +28,17 @@ def _oracle_from_csr(data, dictionary, device):
 
 
 def _run_compare(world, binary, tau, passes=4, n_rows=3000, n_feat=700, lam=0.5, tail=0, seed=3,
-                 fused=False, graph=False, expect_filter=True, server_cta_keys=0):
-    from parameter_server_b200.models.darlin import DarlinConfig, DarlinEngine, run_pass_lockstep
+                 fused=False, graph=False, expect_filter=True, emulated=False, repeat_blocks=False,
+                 grid_per_rank=0):
+    from parameter_server_b200.models.darlin import (DarlinConfig, DarlinEngine, run_pass_emulated,
+                                                     run_pass_lockstep)
     from parameter_server_b200.models.darlin_oracle import OracleServer, run_oracle_pass
     from parameter_server_b200.parallel.comm import run_threads
     from parameter_server_b200.utils.synthetic import make_rcv1_like
     dev = torch.device("cuda:0")
     cfg = DarlinConfig(lambda_l1=lam, max_block_delay=tau, tail_feature_freq=tail,
-                       feature_block_ratio=0.5, seg_len=64, use_graph=graph, seed=seed, fused=fused,
-                       server_cta_keys=server_cta_keys)
+                       feature_block_ratio=0.5, seg_len=64, use_graph=graph, seed=seed,
+                       fused=fused or emulated)
     shards = [make_rcv1_like(n_rows, n_feat, 24.0, seed=seed, shard=r, device=dev, binary=binary)
               for r in range(world)]
 
@@ -63,7 +65,11 @@ def _run_compare(world, binary, tau, passes=4, n_rows=3000, n_feat=700, lam=0.5,
     for it in range(passes):
         order = list(range(len(blocks)))
         rng.shuffle(order)
-        if fused:
+        if repeat_blocks:  # the same block in consecutive steps and two steps apart (a, a, b, a, ...)
+            order = [order[0], order[0], order[1], order[0]] + order
+        if emulated:
+            p = run_pass_emulated(engines, order, thr, reset, grid_per_rank=grid_per_rank)
+        elif fused:
             assert world == 1
             p = e0.run_pass(order, thr, reset)
         else:
@@ -84,6 +90,11 @@ def _run_compare(world, binary, tau, passes=4, n_rows=3000, n_feat=700, lam=0.5,
                           rtol=1e-9, atol=1e-12)
     if expect_filter:
         assert int(torch.isnan(server.w).sum()) > 0, "test should exercise the KKT filter"
+    if emulated:  # every rank's replica is bit-identical to the shards
+        for e in engines:
+            rep = e.w_cache[:dictionary.numel()]
+            assert torch.equal(torch.isnan(rep), torch.isnan(w_dev))
+            assert torch.equal(torch.where(torch.isnan(rep), 0, rep), torch.where(both_nan, 0, w_dev))
     for e in engines:
         e.close()
 
@@ -122,9 +133,24 @@ def test_darlin_fused_large_grid_many_segments():
                  expect_filter=False)
 
 
-def test_darlin_fused_grid_wide_server_phase():
-    # force the "large step" path: shard update shared by all CTAs between grid barriers
-    _run_compare(world=1, binary=False, tau=2, fused=True, server_cta_keys=1)
+# The persistent multi-rank pass (tagged entries, replicated update, flow-control flags): all
+# ranks run side by side in ONE cooperative launch, the code path of the multi-GPU run.
+def test_darlin_multirank_pass_two_ranks():
+    _run_compare(world=2, binary=False, tau=0, emulated=True)
+
+
+def test_darlin_multirank_pass_three_ranks_delay_tail():
+    _run_compare(world=3, binary=False, tau=1, tail=2, emulated=True)
+
+
+def test_darlin_multirank_pass_four_ranks_binary_repeated_blocks():
+    _run_compare(world=4, binary=True, tau=0, lam=2.0, emulated=True, repeat_blocks=True)
+
+
+def test_darlin_multirank_pass_many_segments_small_grid():
+    # more segments than resident warps: phase-1 state parked in the stash
+    _run_compare(world=2, binary=False, tau=1, n_rows=40000, n_feat=300, emulated=True,
+                 expect_filter=False, grid_per_rank=6)
 
 
 def test_darlin_graph_train_decreases_objective(tmp_path):

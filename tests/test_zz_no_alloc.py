@@ -1,8 +1,9 @@
 """psb_darlin_evaluate_noalloc: the progress evaluation for callers that cannot allocate device
 memory (all HBM already committed to the job's own pools, or a thread that must not block on the
 allocator).  The entry point is called straight through the C ABI, as such a caller would, and
-must reproduce psb_darlin_evaluate (caller-provided scratch) on two calls in a row: the second
-call sees the scratch array exactly as the first one left it.
+must reproduce psb_darlin_evaluate (caller-provided scratch) on calls in a row: each later
+call sees the scratch array exactly as the one before left it (also with a larger grid after a
+smaller one, where an old arrival counter lies inside the new range of partial sums).
 
 Collected last on purpose (file name): if it fails under -x, every other test has already run.
 """
@@ -55,7 +56,8 @@ def test_noalloc_evaluate_matches_scratch_version_twice():
     max_grid = lib.psb_darlin_evaluate_noalloc_max_grid()
     assert max_grid >= 148
 
-    for call, (n_rows, n_keys, grid) in enumerate([(200_003, 47_236, 296), (31_111, 1_000, 64)]):
+    for call, (n_rows, n_keys, grid) in enumerate([(200_003, 47_236, 296), (31_111, 1_000, 64),
+                                                 (150_001, 5_000, 512)]):  # smaller, then larger grid on the used array
         wk, sv, ctrl, keep = _structs(n_rows, n_keys, seed=call)
         ref_out = torch.zeros(6, dtype=torch.int64, device="cuda")
         new_out = torch.zeros(6, dtype=torch.int64, device="cuda")
