@@ -233,10 +233,15 @@ def main() -> None:
         f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run"
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
-    dist = None
+    dist, t_nccl = None, 0.0
     if world > 1:
         import torch.distributed as dist
+        t0 = time.time()
         dist.init_process_group("nccl", device_id=dev)
+        dist.all_reduce(torch.zeros(1, device=dev))   # communicator bootstrap is not preprocessing
+        dist.barrier()
+        torch.cuda.synchronize()
+        t_nccl = time.time() - t0
         comm = TorchComm()
     else:
         comm = SingleComm()
@@ -332,7 +337,7 @@ def main() -> None:
                        "ms_per_step_with_copies": res["dev_ms"] / args.steps,
                        "objective_first_last": [res["objs"][0], res["objs"][-1]],
                        "verification": check,
-                       "load_preprocess_s": t_load, "generate_s": t_gen,
+                       "load_preprocess_s": t_load, "generate_s": t_gen, "nccl_bootstrap_s": t_nccl,
                        "time_to_objective": tto, "strong": strong},
             "clocks": res["clocks"],
             "e2e": {"value": e2e, "unit": "examples/s", "h2d_bytes_per_step": h2d,

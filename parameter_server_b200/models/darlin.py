@@ -145,32 +145,53 @@ class DarlinEngine:
         tot = self.comm.allreduce_sum([float(self.n_rows)], dev)
         self.num_ex_global = int(tot[0])
 
+        # K10: sorted unique keys + counts of this worker, per group
+        local = {}
+        for gid in grp_ids:
+            local[gid] = L.unique_count(groups[gid].to(dev).keys)
+        # server key ranges (ref Postmaster::partitionServerKeyRange, postmaster.cc:17-31)
+        if cfg.shard_by == "all":
+            whole = Range.all()
+        else:
+            ends = [(int(u[0].item()) & _M64, int(u[-1].item()) & _M64) for u, _ in local.values() if u.numel()]
+            ends = [e for part in self.comm.gather_obj(ends) for e in part]
+            whole = Range(min(e[0] for e in ends), max(e[1] for e in ends) + 1)
+        self.server_ranges = [whole.even_divide(W, s) for s in range(W)]
+        cuts = torch.tensor([_as_i64(r.begin) for r in self.server_ranges[1:]], dtype=torch.int64, device=dev)
+
         dicts, col_base, info = {}, {}, {}
         ncols = 0
         for gid in grp_ids:
             d = groups[gid].to(dev)
-            # K10: unique keys + counts of this worker; exact global counts replace the
-            # reference's CountMin estimate when the sketch is not requested
-            uniq, cnt = L.unique_count(d.keys)
-            parts = self.comm.gather_var(uniq)
-            cparts = self.comm.gather_var(cnt)
-            allk = torch.cat(parts) if W > 1 else uniq
-            dictionary = L.unique_count(allk)[0] if W > 1 else uniq
+            uniq, cnt = local[gid]
+            if W > 1:
+                # C5 / C6: every worker sends the keys (and counts) of each server's range to that
+                # server only; the owner forms the union, sums the counts, applies the tail
+                # filter, and the shard dictionaries are gathered into the global one.  Nobody
+                # ever holds every worker's key list (ref bcd.h:353-397, shared_parameter.h:121-146).
+                cut = [0] + (L.lower_bound(uniq, cuts).tolist() if uniq.numel() else [0] * (W - 1)) + [uniq.numel()]
+                got_k = self.comm.alltoall_var([uniq[cut[s]:cut[s + 1]].contiguous() for s in range(W)])
+                got_c = self.comm.alltoall_var([cnt[cut[s]:cut[s + 1]].contiguous() for s in range(W)])
+                mine = L.unique_count(torch.cat(got_k))[0]
+            else:
+                got_k, got_c, mine = [uniq], [cnt], uniq
             if cfg.tail_feature_freq > 0 and cfg.tail_filter == "countmin":
-                # ref darlin.h:62-75 + kv_vector.h tail filter: every worker inserts its (key, count)
-                # pairs into the owners' sketch, then asks which of its keys occur often enough
+                # the reference's sketch on the owner: insert every worker's (key, count), then query
                 from ..ops.evaluation import CountMin
-                n = int(max(p.numel() for p in parts) * W * cfg.countmin_n_ratio)
-                cm = CountMin(n, cfg.countmin_k, dev)
-                for p, c in zip(parts, cparts):
-                    cm.insert(p, c.clamp(max=255))
-                dictionary = dictionary[cm.query_gt(dictionary, cfg.tail_feature_freq)].contiguous()
+                n = int(self.comm.allreduce_sum([float(max(p.numel() for p in got_k))], dev)[0] * cfg.countmin_n_ratio)
+                cm = CountMin(max(n, 16), cfg.countmin_k, dev)
+                for p, c in zip(got_k, got_c):
+                    if p.numel():
+                        cm.insert(p, c.clamp(max=255))
+                if mine.numel():
+                    mine = mine[cm.query_gt(mine, cfg.tail_feature_freq)].contiguous()
             elif cfg.tail_feature_freq > 0:
-                total = torch.zeros(dictionary.numel(), dtype=torch.int64, device=dev)
-                for p, c in zip(parts, cparts):
-                    idx = L.lookup_sorted(dictionary, p).long() - 1
-                    total.index_add_(0, idx, c.long())
-                dictionary = dictionary[total > cfg.tail_feature_freq].contiguous()
+                total = torch.zeros(mine.numel(), dtype=torch.int64, device=dev)
+                for p, c in zip(got_k, got_c):
+                    if p.numel():
+                        total.index_add_(0, L.lookup_sorted(mine, p).long() - 1, c.long())
+                mine = mine[total > cfg.tail_feature_freq].contiguous()
+            dictionary = torch.cat([t.to(dev) for t in self.comm.gather_var(mine)]) if W > 1 else mine
             nnz_ele, nnz_ex = float(d.nnz), float((d.row_ptr[1:] > d.row_ptr[:-1]).sum().item())
             s = self.comm.allreduce_sum([nnz_ele, nnz_ex], dev)
             info[gid] = dict(nnz_ele=s[0], nnz_ex=s[1])
@@ -245,14 +266,6 @@ class DarlinEngine:
     def _partition_servers(self) -> None:
         """ref Postmaster::partitionServerKeyRange (postmaster.cc:17-31) + sliceKeyOrderedMsg."""
         cfg, dev, S = self.cfg, self.device, self.world
-        if cfg.shard_by == "all":
-            whole = Range.all()
-        else:
-            lo = min(self._key_at(g, 0) for g in self.grp_ids if self.dicts[g].numel())
-            hi = max(self._key_at(g, self.dicts[g].numel() - 1) + 1
-                     for g in self.grp_ids if self.dicts[g].numel())
-            whole = Range(lo, hi)
-        self.server_ranges = [whole.even_divide(S, s) for s in range(S)]
         bounds = [r.begin for r in self.server_ranges] + [self.server_ranges[-1].end]
         probes = torch.tensor([_as_i64(b) for b in bounds], dtype=torch.int64, device=dev)
         # slice[g][s] = [lo, hi) positions of server s inside group g's dictionary
@@ -278,38 +291,54 @@ class DarlinEngine:
                     col_off[cb + lo:cb + hi] = torch.arange(hi - lo, device=dev) + self.shard_base[(gid, s)]
         self.col_owner, self.col_off = col_owner, col_off
         nb = len(self.blocks)
-        blk_col = torch.zeros(max(nb, 1) * 2, dtype=torch.int64)
-        blk_rng = torch.zeros(max(nb, 1) * 2, dtype=torch.int64)
-        blk_mask = torch.zeros(max(nb, 1), dtype=torch.int32)
-        max_blk_keys = 1
-        for b, (gid, _r, clo, chi) in enumerate(self.blocks):
-            blk_col[2 * b], blk_col[2 * b + 1] = clo, chi
-            plo, phi = clo - self.col_base[gid], chi - self.col_base[gid]
-            mask = 0
-            for s, (lo, hi) in enumerate(self.slices[gid]):
-                a, z = max(plo, lo), min(phi, hi)
-                if z > a:
-                    mask |= 1 << s
-                    if s == self.rank:
-                        base = self.shard_base[(gid, s)]
-                        blk_rng[2 * b], blk_rng[2 * b + 1] = base + a - lo, base + z - lo
-                        max_blk_keys = max(max_blk_keys, z - a)
-            blk_mask[b] = mask
-        cs = self.col_seg.cpu()
-        blk_tab = torch.zeros(max(nb, 1) * 6, dtype=torch.int64)
-        for b in range(nb):
-            lo, hi = int(blk_col[2 * b]), int(blk_col[2 * b + 1])
-            blk_tab[6 * b + 0] = cs[lo]
-            blk_tab[6 * b + 1] = cs[hi] - cs[lo]
-            blk_tab[6 * b + 2] = blk_rng[2 * b]
-            blk_tab[6 * b + 3] = blk_rng[2 * b + 1] - blk_rng[2 * b]
-            blk_tab[6 * b + 4] = int(blk_mask[b])
+        # block x server intersections, vectorised (ref sliceKeyOrderedMsg, message.h:120-159)
+        blk_col = np.zeros((max(nb, 1), 2), dtype=np.int64)
+        blk_rng = np.zeros((max(nb, 1), 2), dtype=np.int64)
+        blk_mask = np.zeros(max(nb, 1), dtype=np.int64)
+        if nb:
+            blk_col[:nb] = np.array([(b[2], b[3]) for b in self.blocks], dtype=np.int64)
+            gids = np.array([b[0] for b in self.blocks])
+            for gid in self.grp_ids:
+                sel = np.nonzero(gids == gid)[0]
+                if sel.size == 0:
+                    continue
+                cb = self.col_base[gid]
+                plo, phi = blk_col[sel, 0] - cb, blk_col[sel, 1] - cb
+                lo_s = np.array([lo for lo, _ in self.slices[gid]], dtype=np.int64)
+                hi_s = np.array([hi for _, hi in self.slices[gid]], dtype=np.int64)
+                a = np.maximum(plo[:, None], lo_s[None, :])
+                z = np.minimum(phi[:, None], hi_s[None, :])
+                inter = z > a
+                blk_mask[sel] = (inter.astype(np.int64) << np.arange(S)[None, :]).sum(1)
+                me = inter[:, self.rank]
+                base = self.shard_base[(gid, self.rank)] - lo_s[self.rank]
+                blk_rng[sel[me], 0] = base + a[me, self.rank]
+                blk_rng[sel[me], 1] = base + z[me, self.rank]
+                # the same for every server (used by the NCCL comparison variant)
+                bases = np.array([self.shard_base[(gid, t)] for t in range(S)], dtype=np.int64) - lo_s
+                rng_all = np.stack([np.where(inter, bases[None, :] + a, 0),
+                                    np.where(inter, bases[None, :] + z, 0)], axis=2)
+                self.blk_srv_rng = getattr(self, "blk_srv_rng", None)
+                if self.blk_srv_rng is None or self.blk_srv_rng.shape[0] != nb:
+                    self.blk_srv_rng = np.zeros((nb, S, 2), dtype=np.int64)
+                self.blk_srv_rng[sel] = rng_all
+        max_blk_keys = int(max(1, (blk_rng[:, 1] - blk_rng[:, 0]).max()))
+        cs = self.col_seg.cpu().numpy()
+        blk_tab = np.zeros((max(nb, 1), 6), dtype=np.int64)
+        blk_tab[:, 0] = cs[blk_col[:, 0]]
+        blk_tab[:, 1] = cs[blk_col[:, 1]] - cs[blk_col[:, 0]]
+        blk_tab[:, 2] = blk_rng[:, 0]
+        blk_tab[:, 3] = blk_rng[:, 1] - blk_rng[:, 0]
+        blk_tab[:, 4] = blk_mask
+        self.max_blk_segs = int(max(1, blk_tab[:, 1].max()))
+        blk_tab = torch.from_numpy(blk_tab.reshape(-1))
+        blk_col = torch.from_numpy(blk_col.reshape(-1))
+        blk_rng = torch.from_numpy(blk_rng.reshape(-1))
+        blk_mask = torch.from_numpy(blk_mask.astype(np.int32))
         self.blk_tab = blk_tab.to(dev)
         self.blk_col, self.blk_rng = blk_col.to(dev), blk_rng.to(dev)
         self.blk_srv_mask = blk_mask.to(dev)
         self.max_blk_keys = max_blk_keys
-        segs = (self.col_seg[blk_col[1::2].to(dev)] - self.col_seg[blk_col[0::2].to(dev)])
-        self.max_blk_segs = int(segs.max().item()) if nb else 1
 
     def _allocate_state(self) -> None:
         cfg, dev, W = self.cfg, self.device, self.world
@@ -452,6 +481,9 @@ class DarlinEngine:
             self.replicated = False
 
     def _enqueue(self, n_steps: int) -> None:
+        if self.cfg.collectives == "nccl":
+            from .darlin_nccl import enqueue_pass_nccl
+            return enqueue_pass_nccl(self, n_steps)
         if self.cfg.fused and self.grid_fused > 0 and (self.world == 1 or self.replicated):
             K.fused_pass(self.wk, self.sv, self.ctrl_dev.data_ptr(), self.order_dev.data_ptr(),
                          self.blk_tab.data_ptr(), n_steps, self.bps, self.grid_fused,
@@ -530,7 +562,7 @@ class DarlinEngine:
         ev[0].record(stream)
         n_steps = self.stage_pass(order, kkt_threshold, reset_kkt_filter, n_prior)
         ev[1].record(stream)
-        if cfg.use_graph:
+        if cfg.use_graph and cfg.collectives != "nccl":
             g = self._graphs.get(n_steps)
             if g is None:
                 g = torch.cuda.CUDAGraph()
@@ -552,7 +584,7 @@ class DarlinEngine:
 
     def capture(self, n_steps: int | None = None) -> None:
         """Capture the pass graph ahead of the first pass (set-up, changes no state)."""
-        if not self.cfg.use_graph:
+        if not self.cfg.use_graph or self.cfg.collectives == "nccl":
             return
         n_steps = n_steps if n_steps is not None else len(self.plan_steps(list(self.blk_order)))
         if n_steps in self._graphs:
@@ -770,6 +802,9 @@ def run_pass_emulated(engines: list, order: list, kkt_threshold: float, reset: b
         p = e.finish_pass(n_steps)
         out = out or p
     return out
+
+
+_M64 = 0xFFFFFFFFFFFFFFFF
 
 
 def _as_i64(u: int) -> int:
