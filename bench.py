@@ -208,7 +208,7 @@ def main() -> None:
     ap.add_argument("--epsilon", type=float, default=1e-4, help="stopping rule (rcv1/batch_l1lr.conf)")
     ap.add_argument("--max-pass", type=int, default=20, help="max_pass_of_data (rcv1/batch_l1lr.conf)")
     ap.add_argument("--block-ratio", type=float, default=4.0)
-    ap.add_argument("--seg-len", type=int, default=256)
+    ap.add_argument("--seg-len", type=int, default=128)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--profile-phases", action="store_true")
     ap.add_argument("--fused-grid", type=int, default=0)
@@ -238,7 +238,11 @@ def main() -> None:
         import torch.distributed as dist
         t0 = time.time()
         dist.init_process_group("nccl", device_id=dev)
-        dist.all_reduce(torch.zeros(1, device=dev))   # communicator bootstrap is not preprocessing
+        # communicator bootstrap (channels of every collective used during set-up) is not preprocessing
+        dist.all_reduce(torch.zeros(1, device=dev))
+        dist.all_to_all_single(torch.zeros(world, device=dev), torch.zeros(world, device=dev))
+        dist.all_gather([torch.zeros(1, device=dev) for _ in range(world)], torch.zeros(1, device=dev))
+        dist.all_gather_object([None] * world, rank)
         dist.barrier()
         torch.cuda.synchronize()
         t_nccl = time.time() - t0
