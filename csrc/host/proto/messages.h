@@ -377,7 +377,7 @@ typedef Pb<ManageAppView> ManageApp;
 class TaskView : public PbView {
  public:
   PB_VIEW(TaskView)
-#define L(X) X(TERMINATE, 1) X(TERMINATE_CONFIRM, 2) X(REPLY, 3) X(MANAGE, 4) X(CALL_CUSTOMER, 5) X(HEARTBEATING, 6)
+#define L(X) X(TERMINATE, 1) X(TERMINATE_CONFIRM, 2) X(REPLY, 3) X(MANAGE, 4) X(CALL_CUSTOMER, 5) X(HEARTBEATING, 6) X(PEER_CREDIT, 7)
   PB_DEFINE_ENUM_IN_CLASS(Type, L)
 #undef L
   PB_ENUM(Type, type, CALL_CUSTOMER)
@@ -398,6 +398,10 @@ class TaskView : public PbView {
   PB_MSG(CallSharedParaView, shared_para)
   PB_MSG(SGDCallView, sgd)
   PB_MSG(BCDCallView, bcd)
+  // PeerVan (system/peer_van.h): value frames left in the sender's device arena
+  // "index:alloc id:offset:length,...", and allocation ids the sender may reuse
+  PB_STRING(peer_frames, "")
+  PB_STRING(peer_credit, "")
 };
 typedef Pb<TaskView> Task;
 

@@ -1,4 +1,5 @@
 #include "system/runtime.h"
+#include "system/peer_van.h"
 #include "util/local_machine.h"
 
 #include <list>
@@ -30,6 +31,13 @@ DEFINE_int32(my_rank, -1, "my rank among MPI peers (mpi launcher)");
 DEFINE_string(interface, "", "network interface (mpi launcher)");
 DEFINE_bool(key_cache, true, "enable caching keys during communication");
 DEFINE_bool(message_compression, true, "snappy-compress every message payload");
+// B200 data plane (no counterpart in the reference)
+DEFINE_string(device, "cpu", "cpu: values in host memory, payloads over the host van; gpu: KV containers "
+                             "keep their values in HBM and value frames travel through CUDA-IPC peer memory");
+DEFINE_int32(gpu, -1, "CUDA device of this node (-1: the number in the node id modulo the device count)");
+DEFINE_int32(peer_arena_mb, 256, "size of this node's staging arena for device value frames");
+DEFINE_string(peer_dir, "", "rendezvous directory of the IPC handles (default /tmp/psb_peer_<scheduler port>)");
+DEFINE_int32(kvmap_capacity, 1 << 20, "slots of a KVMap shard kept in HBM (-device gpu)");
 
 // ---- natural node-id order ---------------------------------------------------------------------
 bool NaturalLess::operator()(const string& a, const string& b) const {
@@ -204,14 +212,25 @@ Filter* RNode::findFilter(const FilterConfigView& conf) {
 }
 void RNode::encodeFilter(const MessagePtr& msg) {
   TaskView tk = msg->task;
-  if (exec_.sys().messageCompression() && msg->memSize() > 0 &&
+  // frames in device memory are never touched by the host: only key filters apply to them
+  bool device_frames = false;
+  for (const auto& v : msg->value) device_frames |= v.onDevice();
+  if (exec_.sys().messageCompression() && msg->memSize() > 0 && !device_frames &&
       !Filter::find(FilterConfigView::COMPRESSING, msg).valid())
     msg->addFilter(FilterConfigView::COMPRESSING);
-  for (int i = 0; i < tk.filter_size(); ++i) findFilter(tk.filter(i))->encode(msg);
+  for (int i = 0; i < tk.filter_size(); ++i) {
+    if (device_frames && tk.filter(i).type() != FilterConfigView::KEY_CACHING) continue;
+    findFilter(tk.filter(i))->encode(msg);
+  }
 }
 void RNode::decodeFilter(const MessagePtr& msg) {
   TaskView tk = msg->task;
-  for (int i = tk.filter_size() - 1; i >= 0; --i) findFilter(tk.filter(i))->decode(msg);
+  bool device_frames = false;
+  for (const auto& v : msg->value) device_frames |= v.onDevice();
+  for (int i = tk.filter_size() - 1; i >= 0; --i) {
+    if (device_frames && tk.filter(i).type() != FilterConfigView::KEY_CACHING) continue;
+    findFilter(tk.filter(i))->decode(msg);
+  }
 }
 MessagePtrList RNode::pendingMsgs() {
   Lock l(mu_);
@@ -755,8 +774,20 @@ void Postoffice::start(const PostofficeOptions& opt) {
   my_role_ = (int)opt_.my_node.role();
   setCurrent(this);
   const bool scheduler = my_role_ == (int)NodeView::SCHEDULER;
-  if (opt_.fabric) yp_.setVan(unique_ptr<Van>(new InprocVan(opt_.fabric)));
-  else yp_.setVan(unique_ptr<Van>(new TcpVan()));
+  unique_ptr<Van> van;
+  if (opt_.fabric) van.reset(new InprocVan(opt_.fabric));
+  else van.reset(new TcpVan());
+  if (FLAGS_device == "gpu") {
+    // the GPU data plane: headers over the van above, device value frames through peer memory
+    int gpu = FLAGS_gpu;
+    if (gpu < 0) {
+      gpu = 0;
+      for (char ch : my_id_) if (ch >= '0' && ch <= '9') gpu = gpu * 10 + (ch - '0');
+    }
+    string dir = FLAGS_peer_dir.empty() ? "/tmp/psb_peer_" + to_string(opt_.scheduler.port()) : FLAGS_peer_dir;
+    van.reset(new PeerVan(std::move(van), gpu, (size_t)std::max(FLAGS_peer_arena_mb, 8) << 20, dir));
+  }
+  yp_.setVan(std::move(van));
   CHECK(yp_.van().init(opt_.my_node)) << "van init failed for " << opt_.my_node.ShortDebugString();
   if (opt_.print_van) yp_.van().enableLog("van_" + my_id_);
   yp_.addNode(opt_.my_node);

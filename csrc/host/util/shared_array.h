@@ -29,6 +29,7 @@ class SArray {
     capacity_ = arr.capacity() * sizeof(W) / sizeof(V);
     ptr_ = arr.pointer();
     data_ = reinterpret_cast<V*>(arr.data());
+    dev_ = arr.onDevice();
   }
   // wrap external memory; deletable=false leaves ownership with the caller
   SArray(V* data, size_t size, bool deletable = true) { reset(data, size, deletable); }
@@ -59,8 +60,22 @@ class SArray {
     r.data_ = data_ + range.begin();
     r.size_ = range.size();
     r.capacity_ = r.size_;
+    r.dev_ = dev_;
     return r;
   }
+
+  // A view of DEVICE memory (HBM, possibly another process' buffer mapped with CUDA IPC): only
+  // pointer arithmetic (segment, reinterpretation, size) is valid on the host, the bytes are
+  // touched by kernels.  `owner` keeps the memory alive; its deleter runs when the last view dies.
+  static SArray<V> wrapDevice(const shared_ptr<char>& owner, V* data, size_t n) {
+    SArray<V> r;
+    r.ptr_ = owner;
+    r.data_ = data;
+    r.size_ = r.capacity_ = n;
+    r.dev_ = true;
+    return r;
+  }
+  bool onDevice() const { return dev_; }
 
   // both arrays must be sorted and duplicate-free
   SArray<V> setIntersection(const SArray<V>& other) const {
@@ -117,6 +132,7 @@ class SArray {
     ptr_.reset();
     data_ = nullptr;
     size_ = capacity_ = 0;
+    dev_ = false;
   }
   void append(const SArray<V>& tail) {
     if (tail.empty()) return;
@@ -233,6 +249,7 @@ class SArray {
   size_t capacity_ = 0;
   V* data_ = nullptr;
   shared_ptr<char> ptr_;
+  bool dev_ = false;
 };
 
 template <typename V>

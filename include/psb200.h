@@ -370,6 +370,39 @@ int psb_kv_bulk_gather_send(const float* val, const int64_t* const* slots_host, 
                             uint64_t seq, uint32_t* done_ctr, void* stream);
 int psb_kv_wait_flags(const uint64_t* flags, int32_t n, uint64_t seq, void* stream);
 
+
+/* ------------------------------------------------------------------------- *
+ *  Device storage of the public KV containers (devkv.cu), used by the host runtime's device
+ *  backend (csrc/host/parameter/kv.h) through dlopen.
+ *  ref: KVVector::setValue/getValue (kv_vector.h:46-93), KVMap (kv_map.h:4-45),
+ *       compAssOp (shared_parameter.h:173-193)
+ * ------------------------------------------------------------------------- */
+enum { PSB_DT_F32 = 0, PSB_DT_F64 = 1, PSB_DT_I32 = 2, PSB_DT_I64 = 3, PSB_DT_U8 = 4 };
+/* ASSIGN plus the reference's Operator enum (param.proto) */
+enum { PSB_OP_ASSIGN = 0, PSB_OP_PLUS = 1, PSB_OP_MINUS = 2, PSB_OP_TIMES = 3, PSB_OP_DIVIDE = 4,
+       PSB_OP_AND = 5, PSB_OP_OR = 6, PSB_OP_XOR = 7 };
+int psb_device_count(int32_t* out);
+int psb_set_device(int32_t dev);
+int psb_stream_create(void** out);
+int psb_stream_destroy(void* stream);
+/* dst[pos[i]*k + c] (op)= src[i*k + c]; pos NULL = contiguous, pos[i] < 0 skipped.  `src` may be a
+ * CUDA-IPC mapping of the sender's staging arena: the payload is read over NVLink while applied. */
+int psb_dkv_apply(void* dst, const int64_t* pos, const void* src, int64_t n, int32_t k,
+                  int32_t dtype, int32_t op, void* stream);
+/* dst[i] = src[pos[i]] for entries of entry_bytes bytes (dst may be a peer mapping); pos[i] < 0 -> 0 */
+int psb_dkv_gather(void* dst, const void* src, const int64_t* pos, int64_t n, int32_t entry_bytes,
+                   void* stream);
+/* pos[i] = index of keys[i] in the sorted unique my_keys, or -1 */
+int psb_dkv_positions(const uint64_t* my_keys, int64_t n_my, const uint64_t* keys, int64_t n,
+                      int64_t* pos, void* stream);
+/* hash map (KVMap): open-addressing key table, capacity a power of two; values live in a caller
+ * array indexed by slot */
+int psb_dmap_clear(uint64_t* table_keys, int64_t cap, void* stream);
+int psb_dmap_slots(uint64_t* table_keys, int64_t cap, const uint64_t* keys, int64_t n, int32_t insert,
+                   int64_t* slot, int32_t* overflow_dev, void* stream);
+int psb_dmap_export(const uint64_t* table_keys, int64_t cap, uint64_t* out_keys, int64_t* out_slot,
+                    uint64_t* count_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
