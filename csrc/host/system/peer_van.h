@@ -190,7 +190,8 @@ class PeerVan : public Van {
     std::mutex mu;
     std::map<string, char*> arenas;
   };
-  static Registry& registry() { static Registry r; return r; }
+  // never destroyed: vans owned by static postoffices are torn down during static destruction
+  static Registry& registry() { static Registry* r = new Registry(); return *r; }
 
   bool locate(const char* p, size_t n, uint64* id, uint64* off) {
     if (p < base_ || p + n > base_ + arena_bytes_) return false;
