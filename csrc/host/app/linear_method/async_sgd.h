@@ -1,54 +1,58 @@
-// Asynchronous minibatch SGD for linear models: FTRL, AdaGrad and plain SGD server updates.
+// Asynchronous minibatch SGD for linear models: FTRL, AdaGrad and plain SGD on the servers.
 // ref src/app/linear_method/async_sgd.h:18-301
-// Fixed relative to the reference: AdaGrad / SGD entries really update (they are TODO no-ops
-// there, :72-99), `ada_grad` selects AdaGrad (the reference's branch is inverted, :136-140),
-// and SGDConfig.max_delay bounds the number of minibatches in flight per worker (declared but
-// never read in the reference, linear.proto:47).
+//
+// Differences from the reference, all towards what it declares but does not do: AdaGrad / SGD
+// really update (TODO no-ops there, :72-99), `ada_grad` selects AdaGrad (inverted there,
+// :136-140), SGDConfig.max_delay bounds the minibatches a worker has in flight (never read
+// there, linear.proto:47), and the pull is tagged for key caching so that the push that follows
+// can travel without its keys (only the push is tagged there, so the cache never hits).
+//
+// Layout: a server-side optimizer is a *rule* (how a gradient changes one coordinate) wrapped
+// by Coordinate<Rule>, which adds the bookkeeping every rule shares; the worker is a pipeline
+// of two stages (request weights, answer with a gradient) with an InFlight window between them.
 #pragma once
-#include "app/linear_method/darlin.h"
+#include "app/linear_method/linear.h"
+#include "app/linear_method/loss.h"
 #include "learner/sgd.h"
 
 namespace PS {
 namespace LM {
 
-class AsyncSGDScheduler : public ISGDScheduler, public LinearMethod {
+class AsyncSGDScheduler : public ISGDScheduler {
  public:
-  AsyncSGDScheduler(const string& name, const ConfigView& conf)
-      : ISGDScheduler(name), LinearMethod(conf) {}
+  AsyncSGDScheduler(const string& name, const ConfigView& conf) : ISGDScheduler(name), conf_(conf) {}
   virtual ~AsyncSGDScheduler() { stopExecutor(); }
   void run() override {
     updateModel(conf_.training_data(), conf_.async_sgd().report_interval());
     if (conf_.has_model_output()) saveModel();
   }
-  double lastLoss() const { return last_loss_; }
-  double lastAUC() const { return last_auc_; }
+
+ private:
+  Config conf_;
 };
 
+// ---- server side: shared state + per-coordinate rules ------------------------------------------------
+// what all coordinates of a shard share: step size schedule, penalty, model statistics
 template <typename V>
 struct SGDState {
   SGDState() {}
-  SGDState(const PenaltyConfigView& h_conf, const LearningRateConfigView& lr_conf) {
-    lr = shared_ptr<LearningRate<V>>(new LearningRate<V>(lr_conf));
-    h = createPenalty<V>(h_conf);
-  }
-  // called once per applied push: report the model statistics to the scheduler
+  SGDState(const PenaltyConfigView& penalty, const LearningRateConfigView& rate)
+      : lr(new LearningRate<V>(rate)), h(createPenalty<V>(penalty)) {}
+  // KVStore calls this after every applied push: the statistics go to the scheduler
   void update() {
     ++iter;
     if (!reporter) return;
-    SGDProgress prog;
-    prog.set_nnz(nnz);
-    prog.set_weight_sum(weight_sum);
-    prog.set_delta_sum(delta_sum);
-    weight_sum = 0;
-    delta_sum = 0;
-    reporter->report(prog);
+    SGDProgress p;
+    p.set_nnz(nnz);
+    p.set_weight_sum(weight_sum);
+    p.set_delta_sum(delta_sum);
+    weight_sum = delta_sum = 0;
+    reporter->report(p);
   }
-  void updateWeight(V new_weight, V old_weight) {
-    if (new_weight == 0 && old_weight != 0) --nnz;
-    else if (new_weight != 0 && old_weight == 0) ++nnz;
-    weight_sum += new_weight * new_weight;
-    V delta = new_weight - old_weight;
-    delta_sum += delta * delta;
+  void moved(V from, V to) {
+    nnz += (to != 0) - (from != 0);
+    weight_sum += to * to;
+    delta_sum += (to - from) * (to - from);
   }
   shared_ptr<LearningRate<V>> lr;
   PenaltyPtr<V> h;
@@ -58,203 +62,215 @@ struct SGDState {
   MonitorSlaver<SGDProgress>* reporter = nullptr;
 };
 
-// w <- prox_h(w - eta g, eta), eta = alpha / (beta + sqrt(sum g^2))
-template <typename V>
-struct AdaGradEntry {
-  void get(V const* data, SGDState<V>* state) {
-    V grad = *data, w_old = weight;
-    sum_sq_grad += grad * grad;
-    V eta = state->lr->eval(sqrt(sum_sq_grad));
-    weight = state->h->proximal(weight - eta * grad, eta);
-    state->updateWeight(weight, w_old);
+// Entry interface of KVStore (get = apply a gradient, put = emit the weight) on top of a rule
+// with `V apply(V w, V grad, SGDState<V>&)` returning the new weight
+template <typename V, class Rule>
+struct Coordinate : Rule {
+  V w = 0;
+  void get(V const* grad, SGDState<V>* s) {
+    const V before = w;
+    w = Rule::apply(before, *grad, *s);
+    s->moved(before, w);
   }
-  void put(V* data, SGDState<V>*) { *data = weight; }
-  V weight = 0, sum_sq_grad = 0;
+  void put(V* out, SGDState<V>*) { *out = w; }
 };
 
-// w <- prox_h(w - eta g, eta), eta = alpha / (beta + sqrt(t))
+// w <- prox(w - eta g, eta) with eta = lr(sqrt(sum of squared gradients of this coordinate))
 template <typename V>
-struct SGDEntry {
-  void get(V const* data, SGDState<V>* state) {
-    V grad = *data, w_old = weight;
-    V eta = state->lr->eval(sqrt((V)(state->iter + 1)));
-    weight = state->h->proximal(weight - eta * grad, eta);
-    state->updateWeight(weight, w_old);
+struct AdaGradRule {
+  V sum_sq = 0;
+  V apply(V w, V g, SGDState<V>& s) {
+    sum_sq += g * g;
+    const V eta = s.lr->eval(sqrt(sum_sq));
+    return s.h->proximal(w - eta * g, eta);
   }
-  void put(V* data, SGDState<V>*) { *data = weight; }
-  V weight = 0;
 };
-
-// FTRL-proximal (ref async_sgd.h:101-124)
+// the same with eta = lr(sqrt(number of pushes applied so far))
 template <typename V>
-struct FTRLEntry {
-  V w = 0, z = 0, sqrt_n = 0;
-  void get(V const* data, SGDState<V>* state) {
-    V w_old = w, grad = *data;
-    V sqrt_n_new = sqrt(sqrt_n * sqrt_n + grad * grad);
-    V sigma = (sqrt_n_new - sqrt_n) / state->lr->alpha();
-    z += grad - sigma * w;
-    sqrt_n = sqrt_n_new;
-    V eta = state->lr->eval(sqrt_n);
-    w = state->h->proximal(-z * eta, eta);
-    state->updateWeight(w, w_old);
+struct PlainRule {
+  V apply(V w, V g, SGDState<V>& s) {
+    const V eta = s.lr->eval(sqrt((V)(s.iter + 1)));
+    return s.h->proximal(w - eta * g, eta);
   }
-  void put(V* data, SGDState<V>*) { *data = w; }
 };
+// FTRL-proximal (ref async_sgd.h:101-124): z accumulates g - sigma w with sigma the growth of
+// sqrt(n) over alpha; the weight is the proximal point of -z eta
+template <typename V>
+struct FTRLRule {
+  V z = 0, root_n = 0;
+  V apply(V w, V g, SGDState<V>& s) {
+    const V grown = sqrt(root_n * root_n + g * g);
+    z += g - (grown - root_n) / s.lr->alpha() * w;
+    root_n = grown;
+    const V eta = s.lr->eval(root_n);
+    return s.h->proximal(-z * eta, eta);
+  }
+};
+template <typename V> using FTRLEntry = Coordinate<V, FTRLRule<V>>;
+template <typename V> using AdaGradEntry = Coordinate<V, AdaGradRule<V>>;
+template <typename V> using SGDEntry = Coordinate<V, PlainRule<V>>;
 
 template <typename V>
-class AsyncSGDServer : public ISGDCompNode, public LinearMethod {
+class AsyncSGDServer : public ISGDCompNode {
  public:
-  AsyncSGDServer(const string& name, const ConfigView& conf) : ISGDCompNode(name), LinearMethod(conf) {
-    SGDConfigView sgd = conf_.async_sgd();
-    if (sgd.algo() == SGDConfigView::FTRL)
-      model_.reset(new KVStore<Key, V, FTRLEntry<V>, SGDState<V>>(name + "_model", name));
-    else if (sgd.ada_grad())
-      model_.reset(new KVStore<Key, V, AdaGradEntry<V>, SGDState<V>>(name + "_model", name));
-    else
-      model_.reset(new KVStore<Key, V, SGDEntry<V>, SGDState<V>>(name + "_model", name));
+  AsyncSGDServer(const string& name, const ConfigView& conf) : ISGDCompNode(name), conf_(conf) {
+    const SGDConfigView sgd = conf_.async_sgd();
+    const string store = name + "_model";
+    if (sgd.algo() == SGDConfigView::FTRL) model_.reset(new KVStore<Key, V, FTRLEntry<V>, SGDState<V>>(store, name));
+    else if (sgd.ada_grad()) model_.reset(new KVStore<Key, V, AdaGradEntry<V>, SGDState<V>>(store, name));
+    else model_.reset(new KVStore<Key, V, SGDEntry<V>, SGDState<V>>(store, name));
   }
   virtual ~AsyncSGDServer() { stopExecutor(); }
 
   void init() override {
-    SGDState<V> state(conf_.penalty(), conf_.learning_rate());
-    state.reporter = &reporter_;
-    model_->setState(state);
-    SGDConfigView sgd = conf_.async_sgd();
+    SGDState<V> shared(conf_.penalty(), conf_.learning_rate());
+    shared.reporter = &reporter_;
+    model_->setState(shared);
+    const SGDConfigView sgd = conf_.async_sgd();
     if (sgd.tail_feature_freq() > 0)
-      model_->setTailFilterSize(0, (int)(sgd.countmin_n() / std::max(1, sys_.yp().num_servers())),
-                                sgd.countmin_k());
+      model_->setTailFilterSize(0, (int)(sgd.countmin_n() / std::max(1, sys_.yp().num_servers())), sgd.countmin_k());
   }
   void process(const MessagePtr& msg) override {
-    if (msg->task.sgd().cmd() == SGDCallView::SAVE_MODEL) saveModel();
-  }
-  void saveModel() {
-    DataConfigView output = conf_.model_output();
-    if (output.format() != DataConfigView::TEXT) return;
-    CHECK(output.file_size());
-    string file = output.file(0) + "_" + myNodeID();
+    if (msg->task.sgd().cmd() != SGDCallView::SAVE_MODEL) return;
+    const DataConfigView out = conf_.model_output();
+    if (out.format() != DataConfigView::TEXT) return;
+    CHECK(out.file_size()) << "model_output has no file";
+    const string file = out.file(0) + "_" + myNodeID();
     model_->writeToFile(file);
     LI << myNodeID() << " written the model to " << file;
   }
 
- protected:
+ private:
+  Config conf_;
   unique_ptr<KVState<Key, SGDState<V>>> model_;
 };
 
-template <typename V>
-class AsyncSGDWorker : public ISGDCompNode, public LinearMethod {
+// ---- worker -------------------------------------------------------------------------------------------------
+// minibatches between "weights requested" and "gradient pushed"; enter() blocks while more than
+// `limit` are in flight (limit < 0: never), drain() waits for all of them
+class InFlight {
  public:
-  AsyncSGDWorker(const string& name, const ConfigView& conf)
-      : ISGDCompNode(name), LinearMethod(conf), model_(name + "_model", name), processed_batch_(0) {
-    loss_ = createLoss<V>(conf_.loss());
-  }
-  virtual ~AsyncSGDWorker() { stopExecutor(); }
-
-  void process(const MessagePtr& msg) override {
-    SGDCallView sgd = msg->task.sgd();
-    if (sgd.cmd() == SGDCallView::UPDATE_MODEL) updateModel(sgd);
-  }
-
-  void updateModel(const SGDCallView& call) {
-    SGDConfigView sgd = conf_.async_sgd();
-    MinibatchReader<V> reader;
-    const int n = std::max(sgd.num_data_pass(), 1);
-    const int m = call.data().file_size();
-    std::vector<int> idx(m);
-    for (int i = 0; i < m; ++i) idx[i] = i;
-    DataConfig data(call.data());
-    data.clear_file();
-    std::mt19937 rng(1234 + myRank());
-    for (int i = 0; i < n; ++i) {  // every pass visits the files in a fresh random order
-      std::shuffle(idx.begin(), idx.end(), rng);
-      for (int j = 0; j < m; ++j) data.add_file(call.data().file(idx[j]));
-    }
-    reader.setReader(data, sgd.minibatch(), sgd.data_buf());
-    reader.setFilter((size_t)sgd.countmin_n(), sgd.countmin_k(), sgd.tail_feature_freq());
-    reader.start();
-
-    // tau: minibatches allowed in flight beyond the current one; unset keeps the reference's
-    // behaviour (unbounded, limited only by the prefetch queue)
-    const int max_delay = sgd.has_max_delay() ? sgd.max_delay() : -1;
-    int id = 0;
-    SArray<Key> key;
-    while (true) {
-      std::pair<MatrixPtr<V>, MatrixPtr<V>> yx;
-      if (!reader.read(yx.first, yx.second, key)) break;
-      if (max_delay >= 0) {  // bounded delay: wait until minibatch id - tau - 1 has been pushed
-        std::unique_lock<std::mutex> l(mu_);
-        cv_.wait(l, [&] { return id - processed_batch_ <= max_delay; });
-      }
-      {
-        Lock l(mu_);
-        data_[id] = yx;
-      }
-      MessagePtr msg(new Message(kServerGroup));
-      msg->setKey(key);
-      msg->task.set_key_channel(id);
-      // caching the keys on the pull lets the following push travel without them (the
-      // reference only tags the push, so its cache never hits, async_sgd.h:228-233 vs :272)
-      msg->addFilter(FilterConfigView::KEY_CACHING);
-      msg->fin_handle = [this, id]() { computeGradient(id); };
-      model_.key(id) = key;
-      model_.pull(msg);
-      ++id;
-    }
+  explicit InFlight(int limit) : limit_(limit) {}
+  void enter() {
     std::unique_lock<std::mutex> l(mu_);
-    cv_.wait(l, [&] { return processed_batch_ >= id; });
+    if (limit_ >= 0) cv_.wait(l, [&] { return started_ - done_ <= limit_; });
+    ++started_;
   }
-
-  // runs on the model customer's executor thread once all servers answered the pull
-  void computeGradient(int id) {
-    MatrixPtr<V> Y, X;
-    {
-      Lock l(mu_);
-      Y = data_[id].first;
-      X = data_[id].second;
-      data_.erase(id);
-    }
-    CHECK_EQ(X->rows(), Y->rows());
-    SArray<V> w = model_.value(id);
-    if (w.size() != X->cols()) {  // nothing pulled (all keys new on empty servers)
-      w.resize(X->cols());
-      w.setZero();
-    }
-    SArray<V> Xw = X->times(w);
-    if (getenv("PSB_DEBUG_SGD")) fprintf(stderr, "dbg id=%d rows=%zu cols=%zu nnz=%zu |w|0=%zu wsum=%g Xw0=%g y0=%g keys=%zu\n", id, X->rows(), X->cols(), X->nnz(), w.nnz(), w.sum(), (double)Xw[0], (double)Y->value()[0], model_.key(id).size());
-    SGDProgress prog;
-    prog.add_objective(loss_->evaluate(Y->value(), Xw));
-    prog.add_auc(Evaluation<V>::auc(Y->value(), Xw));
-    prog.add_accuracy(Evaluation<V>::accuracy(Y->value(), Xw));
-    prog.set_num_examples_processed(Xw.size());
-    reporter_.report(prog);
-
-    SArray<V> grad(X->cols());
-    grad.setZero();
-    loss_->compute(Y->value(), X, Xw, grad);
-
-    MessagePtr msg(new Message(kServerGroup));
-    msg->setKey(model_.key(id));
-    msg->addValue(grad);
-    msg->task.set_key_channel(id);
-    msg->addFilter(FilterConfigView::KEY_CACHING).set_clear_cache_if_done(true);
-    int nbytes = conf_.async_sgd().fixing_float_by_nbytes();
-    if (nbytes) msg->addFilter(FilterConfigView::FIXING_FLOAT).add_fixed_point().set_num_bytes(nbytes);
-    model_.push(msg);
-    model_.clear(id);
-    {
-      Lock l(mu_);
-      ++processed_batch_;
-    }
+  void leave() {
+    { Lock l(mu_); ++done_; }
     cv_.notify_all();
+  }
+  void drain() {
+    std::unique_lock<std::mutex> l(mu_);
+    cv_.wait(l, [&] { return done_ >= started_; });
   }
 
  private:
-  KVVector<Key, V> model_;
-  LossPtr<V> loss_;
-  std::unordered_map<int, std::pair<MatrixPtr<V>, MatrixPtr<V>>> data_;
   std::mutex mu_;
   std::condition_variable cv_;
-  int processed_batch_;
+  int limit_, started_ = 0, done_ = 0;
+};
+
+template <typename V>
+class AsyncSGDWorker : public ISGDCompNode {
+ public:
+  AsyncSGDWorker(const string& name, const ConfigView& conf)
+      : ISGDCompNode(name), conf_(conf), model_(name + "_model", name), loss_(createLoss<V>(conf_.loss())) {}
+  virtual ~AsyncSGDWorker() { stopExecutor(); }
+
+  void process(const MessagePtr& msg) override {
+    const SGDCallView call = msg->task.sgd();
+    if (call.cmd() == SGDCallView::UPDATE_MODEL) train(call.data());
+  }
+
+ private:
+  // ref async_sgd.h:197-239
+  void train(const DataConfigView& my_files) {
+    const SGDConfigView sgd = conf_.async_sgd();
+    MinibatchSource<V> source;
+    source.open(epochs(my_files, std::max(sgd.num_data_pass(), 1)), sgd.minibatch(), sgd.data_buf());
+    source.dropRareKeys((size_t)sgd.countmin_n(), sgd.countmin_k(), sgd.tail_feature_freq());
+    source.start();
+    // an unset max_delay keeps the reference's behaviour: bounded by the prefetch queue only
+    InFlight window(sgd.has_max_delay() ? sgd.max_delay() : -1);
+    window_ = &window;
+    Minibatch<V> mb;
+    for (int id = 0; source.next(&mb); ++id) {
+      window.enter();
+      { Lock l(mu_); waiting_[id] = mb; }
+      requestWeights(id, mb.keys);
+    }
+    window.drain();
+    window_ = nullptr;
+  }
+
+  // the files of one pass, visited in a fresh random order in every pass
+  DataConfig epochs(const DataConfigView& files, int passes) {
+    DataConfig all(files);
+    all.clear_file();
+    std::vector<int> order(files.file_size());
+    for (size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
+    std::mt19937 rng(1234 + myRank());
+    for (int p = 0; p < passes; ++p) {
+      std::shuffle(order.begin(), order.end(), rng);
+      for (int i : order) all.add_file(files.file(i));
+    }
+    return all;
+  }
+
+  // stage 1: pull the weights of the minibatch's keys on channel `id`
+  void requestWeights(int id, const SArray<Key>& keys) {
+    MessagePtr ask(new Message(kServerGroup));
+    ask->setKey(keys);
+    ask->task.set_key_channel(id);
+    ask->addFilter(FilterConfigView::KEY_CACHING);
+    ask->fin_handle = [this, id]() { answerWithGradient(id); };
+    model_.key(id) = keys;
+    model_.pull(ask);
+  }
+
+  // stage 2, on the model customer's executor thread once every server answered: margins,
+  // progress report, gradient, push.  ref async_sgd.h:241-289
+  void answerWithGradient(int id) {
+    Minibatch<V> mb;
+    {
+      Lock l(mu_);
+      auto it = waiting_.find(id);
+      mb = it->second;
+      waiting_.erase(it);
+    }
+    CHECK_EQ(mb.X->rows(), mb.Y->rows());
+    SArray<V> w = model_.value(id);
+    if (w.size() != mb.X->cols()) w = SArray<V>(mb.X->cols(), 0);  // nothing came back: all keys are new
+    const SArray<V> margin = mb.X->times(w);
+
+    SGDProgress seen;
+    seen.add_objective(loss_->evaluate(mb.Y->value(), margin));
+    seen.add_auc(Evaluation<V>::auc(mb.Y->value(), margin));
+    seen.add_accuracy(Evaluation<V>::accuracy(mb.Y->value(), margin));
+    seen.set_num_examples_processed(margin.size());
+    reporter_.report(seen);
+
+    SArray<V> grad(mb.X->cols(), 0);
+    loss_->compute(mb.Y->value(), mb.X, margin, grad);
+    MessagePtr give(new Message(kServerGroup));
+    give->setKey(model_.key(id));
+    give->addValue(grad);
+    give->task.set_key_channel(id);
+    give->addFilter(FilterConfigView::KEY_CACHING).set_clear_cache_if_done(true);
+    if (const int nbytes = conf_.async_sgd().fixing_float_by_nbytes())
+      give->addFilter(FilterConfigView::FIXING_FLOAT).add_fixed_point().set_num_bytes(nbytes);
+    model_.push(give);
+    model_.clear(id);
+    window_->leave();
+  }
+
+  Config conf_;
+  KVVector<Key, V> model_;
+  LossPtr<V> loss_;
+  std::mutex mu_;
+  std::unordered_map<int, Minibatch<V>> waiting_;
+  InFlight* window_ = nullptr;
 };
 
 }  // namespace LM

@@ -1,7 +1,15 @@
-// Darlin: delayed block proximal gradient for L1 logistic regression — host (CPU) roles.
-// ref src/app/linear_method/darlin.h:12-514
-// The same algorithm on the device: csrc/cuda/darlin.cu (kernels) driven by
-// parameter_server_b200/models/darlin.py; tests compare both against one oracle.
+// Darlin: delayed block proximal gradient for L1 logistic regression, host roles.
+// ref src/app/linear_method/darlin.h:12-514 (the arithmetic), src/learner/bcd.h (the roles)
+//
+// The arithmetic lives in DarlinMath as three free-standing kernels over plain arrays -
+// column gradients, the proximal Newton step of a coordinate range, the dual rescaling - so
+// that the roles below only move data: the scheduler issues the passes (PassIssuer, StopRule),
+// the worker turns a block into (G, U) and a pulled weight block into a dual update, the server
+// turns summed (G, U) into new weights.  The device engine runs the same three kernels as
+// csrc/cuda/darlin.cu; tests compare both against one PyTorch oracle.
+//
+// With -device gpu the model shards are KVBufferedVector columns in HBM and the (G, U) / weight
+// frames travel through the PeerVan; the math of this file stays on the host.
 #pragma once
 #include "app/linear_method/loss.h"
 #include "learner/bcd.h"
@@ -11,393 +19,395 @@ namespace PS {
 namespace LM {
 typedef double Real;
 
-class LinearMethod {
- public:
-  explicit LinearMethod(const ConfigView& conf) : conf_(conf) {}
-  virtual ~LinearMethod() {}
+// ---- the numerical core -----------------------------------------------------------------------------
+struct DarlinMath {
+  // trust region of a coordinate after it moved by d (ref darlin.h:23-25)
+  static Real trustRegion(Real delta_max, Real d) { return std::min(delta_max, 2 * fabs(d) + .1); }
 
- protected:
-  Config conf_;
-};
-
-class DarlinCommon {
- protected:
-  static Real newDelta(Real delta_max, Real delta_w) {
-    return std::min(delta_max, 2 * fabs(delta_w) + .1);
+  // per active column j of [lo, hi):  g_j = -sum_i y_i tau_i x_ij
+  //                                  u_j = sum_i min(tau_i (1 - tau_i) e^{|x_ij| delta_j}, 1/4) x_ij^2
+  // with tau_i = 1 / (1 + dual_i).  Inactive columns get the NaN mark.  G, U are indexed from lo.
+  // ref darlin.h:381-427
+  template <bool kBinary>
+  static void columnGradients(const SparseMatrix<uint32, Real>& X, const Real* y, const Real* dual,
+                              const Bitmap& active, const Real* delta, size_t lo, size_t hi, Real* G, Real* U) {
+    const size_t* colp = X.offset().data();
+    const uint32* row = X.index().data();
+    const Real* val = X.value().data();
+    for (size_t j = lo; j < hi; ++j) {
+      Real& g = G[j - lo];
+      Real& u = U[j - lo];
+      if (!active.test(j)) {
+        SparseFilter::mark(&g);
+        SparseFilter::mark(&u);
+        continue;
+      }
+      g = u = 0;
+      const Real stretch = kBinary ? exp(delta[j]) : delta[j];
+      for (size_t e = colp[j]; e < colp[j + 1]; ++e) {
+        const uint32 i = row[e];
+        const Real tau = 1 / (1 + dual[i]);
+        const Real curv = tau * (1 - tau);
+        if (kBinary) {
+          g -= y[i] * tau;
+          u += std::min(curv * stretch, .25);
+        } else {
+          const Real x = val[e];
+          g -= y[i] * tau * x;
+          u += std::min(curv * exp(fabs(x) * stretch), .25) * x * x;
+        }
+      }
+    }
   }
-  std::unordered_map<int, Bitmap> active_set_;
-  std::unordered_map<int, SArray<Real>> delta_;
-  SparseFilter kkt_filter_;
-  Real kkt_filter_threshold_ = 1e20;
+
+  struct StepParams {
+    Real lambda, eta, delta_max, kkt_threshold;
+  };
+  // coordinates [first, first + n) of a shard: soft-thresholded Newton step inside the trust
+  // region; a zero weight whose gradient sits well inside [-lambda, lambda] leaves the active set
+  // (KKT filter) and is marked NaN.  Returns the largest KKT violation seen.  ref darlin.h:206-246
+  static Real proximalStep(const StepParams& p, size_t first, size_t n, const Real* G, const Real* U,
+                           Real* w, Real* delta, Bitmap* active) {
+    Real worst = 0;
+    for (size_t i = 0; i < n; ++i) {
+      const size_t k = first + i;
+      if (!active->test(k)) continue;
+      const Real u = U[i] / p.eta + 1e-10;
+      const Real up = G[i] + p.lambda, down = G[i] - p.lambda;  // one-sided gradients at w
+      Real& wk = w[k];
+      if (wk == 0) {
+        if (up < 0) worst = std::max(worst, -up);
+        else if (down > 0) worst = std::max(worst, down);
+        else if (up > p.kkt_threshold && down < -p.kkt_threshold) {
+          active->clear(k);
+          SparseFilter::mark(&wk);
+          continue;
+        }
+      }
+      Real d = -wk;  // lands on zero unless one side's Newton step stays on its side
+      if (up <= u * wk) d = -up / u;
+      else if (down >= u * wk) d = -down / u;
+      d = std::max(-delta[k], std::min(delta[k], d));
+      delta[k] = trustRegion(p.delta_max, d);
+      wk += d;
+    }
+    return worst;
+  }
+
+  // rows [r_lo, r_hi) of dual *= exp(y_i dw_j x_ij) over the columns of the block (dw indexed
+  // from lo).  Threads own disjoint row slices, so there is nothing to lock.  ref darlin.h:472-502
+  template <bool kBinary>
+  static void rescaleDual(const SparseMatrix<uint32, Real>& X, const Real* y, const Bitmap& active,
+                          const Real* dw, size_t lo, size_t hi, size_t r_lo, size_t r_hi, Real* dual) {
+    const size_t* colp = X.offset().data();
+    const uint32* row = X.index().data();
+    const Real* val = X.value().data();
+    for (size_t j = lo; j < hi; ++j) {
+      const Real d = dw[j - lo];
+      if (d == 0 || !active.test(j)) continue;
+      for (size_t e = colp[j]; e < colp[j + 1]; ++e) {
+        const uint32 i = row[e];
+        if (i < r_lo || i >= r_hi) continue;
+        dual[i] *= exp(y[i] * d * (kBinary ? 1 : val[e]));
+      }
+    }
+  }
 };
 
-// ---------------------------------------------------------------------------------------------------
-class DarlinScheduler : public BCDScheduler, DarlinCommon, LinearMethod {
+// the coordinate state a server shard and a worker both keep per feature group
+struct CoordinateState {
+  Bitmap active;
+  SArray<Real> delta;
+  void reset(size_t n, Real delta_init) {
+    active.resize(n, true);
+    delta = SArray<Real>(n, delta_init);
+  }
+};
+
+// ---- scheduler ------------------------------------------------------------------------------------------
+// "stop when the relative objective change stayed below epsilon for two passes in a row, the
+// second of which ran over all coordinates again" (ref darlin.h:103-118)
+class StopRule {
  public:
-  DarlinScheduler(const string& name, const ConfigView& conf)
-      : BCDScheduler(name, conf.darlin()), LinearMethod(conf) {}
+  explicit StopRule(Real epsilon) : eps_(epsilon) {}
+  // returns true when training should stop; resetFilter() tells how to run the next pass
+  bool after(Real relative_objective) {
+    const bool small = relative_objective > 0 && relative_objective <= eps_;
+    const bool stop = small && reset_;
+    reset_ = small;
+    return stop;
+  }
+  bool resetFilter() const { return reset_; }
+
+ private:
+  Real eps_;
+  bool reset_ = false;
+};
+
+class DarlinScheduler : public BCDScheduler {
+ public:
+  DarlinScheduler(const string& name, const ConfigView& conf) : BCDScheduler(name, conf.darlin()), conf_(conf) {
+    board_.insertColumn(1, ProgressBoard::Column{
+        {"|      KKT filter     ", "| threshold  #activet ", "+---------------------"},
+        [this](int, const BCDProgress& p) {
+          return ProgressBoard::fmt("| %.1e %11llu ", kkt_threshold_, (unsigned long long)p.nnz_active_set());
+        }});
+  }
   virtual ~DarlinScheduler() { stopExecutor(); }
 
   void run() override {
-    CHECK_EQ((int)conf_.loss().type(), (int)LossConfigView::LOGIT);
-    CHECK_EQ((int)conf_.penalty().type(), (int)PenaltyConfigView::L1);
+    CHECK_EQ((int)conf_.loss().type(), (int)LossConfigView::LOGIT) << "Darlin is logistic loss only";
+    CHECK_EQ((int)conf_.penalty().type(), (int)PenaltyConfigView::L1) << "Darlin is L1 only";
     LI << "Train l_1 logistic regression by block coordinate descent";
     loadTrainingData(conf_.training_data());
     divideFeatureBlocks();
+    const BCDConfigView darlin = conf_.darlin();
+    tau_ = darlin.max_block_delay();
+    LI << "Maximal allowed delay: " << tau_;
+    if (!darlin.random_feature_block_order()) LI << "Warning: Randomized block order often acclerates the convergence.";
 
-    BCDConfigView darlin = conf_.darlin();
-    const int tau = darlin.max_block_delay();
-    LI << "Maximal allowed delay: " << tau;
-    const bool random_blk_order = darlin.random_feature_block_order();
-    if (!random_blk_order) LI << "Warning: Randomized block order often acclerates the convergence.";
-    kkt_filter_threshold_ = 1e20;
-    bool reset_kkt_filter = false;
-
-    const int max_iter = darlin.max_pass_of_data();
-    RNodePtr pool = port(kCompGroup);
-    // a timestamp large enough not to collide with the preprocessing stage
-    int time = std::max(10000, pool->time() + (int)fea_grp_.size() * time_ratio_);
-    const int first_time = time + 1;
-    for (int iter = 0; iter < max_iter; ++iter) {
-      std::vector<int> order = blk_order_;
-      if (random_blk_order) std::shuffle(order.begin(), order.end(), rng_);
-      if (iter == 0) order.insert(order.begin(), prior_blk_order_.begin(), prior_blk_order_.end());
-
-      for (size_t i = 0; i < order.size(); ++i) {
-        Task update;
-        BCDCallView cmd = update.mutable_bcd();
-        cmd.set_cmd(BCDCallView::UPDATE_MODEL);
-        if (i == 0) {  // the KKT filter threshold travels with the first block of a pass
-          cmd.set_kkt_filter_threshold(kkt_filter_threshold_);
-          if (reset_kkt_filter) cmd.set_reset_kkt_filter(true);
-        }
-        const auto& blk = fea_blk_[order[i]];
-        cmd.mutable_key().from(blk.second);
-        cmd.add_fea_grp(blk.first);
-        update.set_time(time + 1);
-        // bounded delay: block t+1 may start once block t-tau has finished on that node
-        int wait_time = time - tau;
-        if (iter == 0 && i < prior_blk_order_.size()) wait_time = time;  // no delay for priors
-        if (wait_time < first_time) wait_time = Message::kInvalidTime;
-        update.add_wait_time(wait_time);
-        time = pool->submit(update);
+    nodes_ = port(kCompGroup);
+    // block tasks start well above the timestamps the preprocessing used
+    time_ = std::max(10000, nodes_->time() + (int)fea_grp_.size() * BcdClock::kStride);
+    first_ = time_ + 1;
+    StopRule rule(darlin.epsilon());
+    const int passes = darlin.max_pass_of_data();
+    for (int iter = 0; iter < passes; ++iter) {
+      issuePass(iter, rule.resetFilter());
+      const BCDProgress row = board_.row(iter);
+      board_.print(iter);
+      kkt_threshold_ = row.violation() / (Real)train_info_.num_ex() * bcd_conf_.kkt_filter_threshold_ratio();
+      if (rule.after(row.relative_obj())) {
+        LI << "Stopped: relative objective <= " << darlin.epsilon();
+        break;
       }
-
-      Task eval;
-      eval.mutable_bcd().set_cmd(BCDCallView::EVALUATE_PROGRESS);
-      if (time - tau >= first_time) eval.add_wait_time(time - tau);
-      time = pool->submitAndWait(eval, [this, iter]() { mergeProgress(iter); });
-      showProgress(iter);
-
-      Real vio = g_progress_[iter].violation();
-      Real ratio = bcd_conf_.kkt_filter_threshold_ratio();
-      kkt_filter_threshold_ = vio / (Real)g_train_info_.num_ex() * ratio;
-
-      Real rel = g_progress_[iter].relative_obj();
-      if (rel > 0 && rel <= darlin.epsilon()) {
-        if (reset_kkt_filter) {
-          LI << "Stopped: relative objective <= " << darlin.epsilon();
-          break;
-        }
-        reset_kkt_filter = true;  // one more pass over all coordinates before stopping
-      } else {
-        reset_kkt_filter = false;
-      }
-      if (iter == max_iter - 1) LI << "Reached maximal " << max_iter << " data passes";
+      if (iter + 1 == passes) LI << "Reached maximal " << passes << " data passes";
     }
     if (conf_.has_model_output()) saveModel(conf_.model_output());
   }
 
- protected:
-  void showKKTFilter(int iter) {
-    if (iter == -3) fprintf(stderr, "|      KKT filter     ");
-    else if (iter == -2) fprintf(stderr, "| threshold  #activet ");
-    else if (iter == -1) fprintf(stderr, "+---------------------");
-    else fprintf(stderr, "| %.1e %11llu ", kkt_filter_threshold_,
-                 (unsigned long long)g_progress_[iter].nnz_active_set());
-  }
-  void showProgress(int iter) {
-    int s = iter == 0 ? -3 : iter;
-    for (int i = s; i <= iter; ++i) {
-      showObjective(i);
-      showKKTFilter(i);
-      showTime(i);
+ private:
+  // one UPDATE_MODEL per block, each allowed to start once the block tau steps earlier has
+  // finished on the receiving node (prior blocks: no delay), then EVALUATE_PROGRESS behind the
+  // same bound.  ref darlin.h:58-103
+  void issuePass(int iter, bool reset_filter) {
+    const std::vector<int> order = planner_.pass(iter, conf_.darlin().random_feature_block_order(), &rng_);
+    const size_t n_prior = planner_.numPrior(iter);
+    for (size_t i = 0; i < order.size(); ++i) {
+      const FeatureBlock& blk = planner_[order[i]];
+      Task step;
+      BCDCallView call = step.mutable_bcd();
+      call.set_cmd(BCDCallView::UPDATE_MODEL);
+      call.mutable_key().from(blk.keys);
+      call.add_fea_grp(blk.group);
+      if (i == 0) {  // per-pass settings ride on the first block
+        call.set_kkt_filter_threshold(kkt_threshold_);
+        if (reset_filter) call.set_reset_kkt_filter(true);
+      }
+      step.set_time(time_ + 1);
+      step.add_wait_time(dependency(i < n_prior ? 0 : tau_));
+      time_ = nodes_->submit(step);
     }
+    Task eval;
+    eval.mutable_bcd().set_cmd(BCDCallView::EVALUATE_PROGRESS);
+    const int dep = dependency(tau_);
+    if (dep != Message::kInvalidTime) eval.add_wait_time(dep);
+    time_ = nodes_->submitAndWait(eval, [this, iter]() { mergeProgress(iter); });
   }
+  // the task `delay` steps before the next one, if this run issued it
+  int dependency(int delay) const { return time_ - delay >= first_ ? time_ - delay : Message::kInvalidTime; }
+
+  Config conf_;
+  RNodePtr nodes_;
+  int time_ = 0, first_ = 0, tau_ = 0;
+  Real kkt_threshold_ = 1e20;
 };
 
-// ---------------------------------------------------------------------------------------------------
-class DarlinServer : public BCDServer<Real>, DarlinCommon, LinearMethod {
+// ---- server --------------------------------------------------------------------------------------------
+class DarlinServer : public BCDServer<Real> {
  public:
-  DarlinServer(const string& name, const ConfigView& conf)
-      : BCDServer<Real>(name, conf.darlin()), LinearMethod(conf) {}
+  DarlinServer(const string& name, const ConfigView& conf) : BCDServer<Real>(name, conf.darlin()), conf_(conf) {}
   virtual ~DarlinServer() { stopExecutor(); }
 
  protected:
   void preprocessData(int time, const BCDCallView& call) override {
     BCDServer<Real>::preprocessData(time, call);
-    for (int grp : fea_grp_) {
-      size_t n = model_.key(grp).size();
-      active_set_[grp].resize(n, true);
-      delta_[grp].resize(n);
-      delta_[grp].setValue(bcd_conf_.delta_init_value());
-    }
+    for (int g : fea_grp_) state_[g].reset(model_.key(g).size(), bcd_conf_.delta_init_value());
   }
 
+  // ref darlin.h:175-204
   void updateModel(int time, const BCDCallView& call) override {
-    if (call.has_kkt_filter_threshold()) {
-      kkt_filter_threshold_ = call.kkt_filter_threshold();
+    if (call.has_kkt_filter_threshold()) {  // first block of a pass
+      kkt_threshold_ = call.kkt_filter_threshold();
       violation_ = 0;
     }
     if (call.reset_kkt_filter())
-      for (int grp : fea_grp_) active_set_[grp].fill(true);
+      for (int g : fea_grp_) state_[g].active.fill(true);
     CHECK_EQ(call.fea_grp_size(), 1);
-    int grp = call.fea_grp(0);
-    Range<Key> g_key_range = call.key().to<Key>();
-    SizeR col_range = model_.find(grp, g_key_range);
-    // none of my business
-    if (myKeyRange().setIntersection(g_key_range).empty()) return;
-    // every worker's gradient for this block has been merged into the buffer
-    model_.waitInMsg(kWorkerGroup, time);
-    if (!col_range.empty()) {
-      auto data = model_.received(time);
-      CHECK_EQ(col_range, data.first);
-      CHECK_EQ(data.second.size(), (size_t)2);
-      updateWeight(grp, col_range, data.second[0], data.second[1]);
-    }
-    model_.finish(kWorkerGroup, time + 1);  // releases the workers' pulls
-  }
-
-  // proximal Newton step per coordinate with a trust region and the KKT filter
-  void updateWeight(int grp, SizeR range, SArray<Real> G, SArray<Real> U) {
-    CHECK_EQ(G.size(), range.size());
-    CHECK_EQ(U.size(), range.size());
-    const Real eta = conf_.learning_rate().alpha();
-    const Real lambda = conf_.penalty().lambda(0);
-    const Real delta_max = bcd_conf_.delta_max_value();
-    SArray<Real>& value = model_.value(grp);
-    Bitmap& active = active_set_[grp];
-    SArray<Real>& delta = delta_[grp];
-    for (size_t i = 0; i < range.size(); ++i) {
-      const size_t k = i + range.begin();
-      if (!active.test(k)) continue;
-      const Real g = G[i], u = U[i] / eta + 1e-10;
-      const Real g_pos = g + lambda, g_neg = g - lambda;
-      Real& w = value[k];
-      Real d = -w, vio = 0;
-      if (w == 0) {
-        if (g_pos < 0) {
-          vio = -g_pos;
-        } else if (g_neg > 0) {
-          vio = g_neg;
-        } else if (g_pos > kkt_filter_threshold_ && g_neg < -kkt_filter_threshold_) {
-          active.clear(k);
-          kkt_filter_.mark(&w);
-          continue;
-        }
-      }
+    const int grp = call.fea_grp(0);
+    const Range<Key> block = call.key().to<Key>();
+    if (myKeyRange().setIntersection(block).empty()) return;  // the block lies outside my shard
+    const SizeR mine = model_.find(grp, block);
+    model_.waitInMsg(kWorkerGroup, time);  // every worker's (G, U) has been summed into the buffer
+    if (!mine.empty()) {
+      auto sums = model_.receivedOnHost(time);
+      CHECK_EQ(sums.first, mine);
+      CHECK_EQ(sums.second.size(), (size_t)2);
+      CHECK_EQ(sums.second[0].size(), mine.size());
+      CoordinateState& st = state_[grp];
+      const DarlinMath::StepParams p{conf_.penalty().lambda(0), conf_.learning_rate().alpha(),
+                                     bcd_conf_.delta_max_value(), kkt_threshold_};
+      const Real vio = DarlinMath::proximalStep(p, mine.begin(), mine.size(), sums.second[0].data(),
+                                                sums.second[1].data(), model_.value(grp).data(),
+                                                st.delta.data(), &st.active);
       violation_ = std::max(violation_, vio);
-      if (g_pos <= u * w) d = -g_pos / u;
-      else if (g_neg >= u * w) d = -g_neg / u;
-      d = std::min(delta[k], std::max(-delta[k], d));
-      delta[k] = newDelta(delta_max, d);
-      w += d;
     }
+    model_.finish(kWorkerGroup, BcdClock::updated(time));  // lets the workers' pulls through
   }
 
+  // ref darlin.h:248-265
   void evaluate(BCDProgress* prog) override {
-    size_t nnz_w = 0, nnz_as = 0;
-    Real objv = 0;
-    for (int grp : fea_grp_) {
-      const SArray<Real>& value = model_.value(grp);
-      for (size_t i = 0; i < value.size(); ++i) {
-        Real w = value[i];
-        if (kkt_filter_.marked(w) || w == 0) continue;
-        ++nnz_w;
-        objv += fabs(w);
-      }
-      nnz_as += active_set_[grp].nnz();
+    size_t nnz = 0, n_active = 0;
+    Real l1 = 0;
+    for (int g : fea_grp_) {
+      for (Real w : model_.value(g))
+        if (w != 0 && !SparseFilter::marked(w)) { ++nnz; l1 += fabs(w); }
+      n_active += state_[g].active.nnz();
     }
-    prog->set_objective(objv * conf_.penalty().lambda(0));
-    prog->set_nnz_w(nnz_w);
+    prog->set_objective(l1 * conf_.penalty().lambda(0));
+    prog->set_nnz_w(nnz);
     prog->set_violation(violation_);
-    prog->set_nnz_active_set(nnz_as);
+    prog->set_nnz_active_set(n_active);
   }
 
-  Real violation_ = 0;
+ private:
+  Config conf_;
+  std::unordered_map<int, CoordinateState> state_;
+  Real kkt_threshold_ = 1e20, violation_ = 0;
 };
 
-// ---------------------------------------------------------------------------------------------------
-class DarlinWorker : public BCDWorker<Real>, DarlinCommon, LinearMethod {
+// ---- worker --------------------------------------------------------------------------------------------
+class DarlinWorker : public BCDWorker<Real> {
  public:
-  DarlinWorker(const string& name, const ConfigView& conf)
-      : BCDWorker<Real>(name, conf.darlin()), LinearMethod(conf) {}
+  DarlinWorker(const string& name, const ConfigView& conf) : BCDWorker<Real>(name, conf.darlin()), conf_(conf) {}
   virtual ~DarlinWorker() { stopExecutor(); }
 
  protected:
   void preprocessData(int time, const BCDCallView& call) override {
     BCDWorker<Real>::preprocessData(time, call);
-    // dual_ = exp(y .* (X w)); with zero initial weights that is all ones
-    if (bcd_conf_.init_w().type() == ParameterInitConfigView::ZERO) {
-      dual_.setValue(1);
-    } else {
-      for (size_t i = 0; i < dual_.size(); ++i) dual_[i] = exp(y_[i] * dual_[i]);
-    }
-    for (int grp : fea_grp_) {
-      size_t n = model_.key(grp).size();
-      active_set_[grp].resize(n, true);
-      delta_[grp].resize(n);
-      delta_[grp].setValue(bcd_conf_.delta_init_value());
-    }
+    // BCDWorker left X w in dual_; Darlin keeps exp(y .* X w)
+    for (size_t i = 0; i < dual_.size(); ++i) dual_[i] = exp(y_[i] * dual_[i]);
+    for (int g : fea_grp_) state_[g].reset(model_.key(g).size(), bcd_conf_.delta_init_value());
   }
 
-  void computeGradient(int time, const BCDCallView& call, MessagePtr msg) override {
+  // a block on the worker: push (G, U) at `time`, then pull the new weights behind the server's
+  // "updated" mark; the scheduler's task is finished by the pull's callback.  ref darlin.h:297-342
+  void computeGradient(int time, const BCDCallView& call, MessagePtr task) override {
     if (call.reset_kkt_filter())
-      for (int grp : fea_grp_) active_set_[grp].fill(true);
+      for (int g : fea_grp_) state_[g].active.fill(true);
     CHECK_EQ(call.fea_grp_size(), 1);
-    int grp = call.fea_grp(0);
-    Range<Key> g_key_range = call.key().to<Key>();
-    SizeR col_range = model_.find(grp, g_key_range);
-    computeAndPushGradient(time, g_key_range, grp, col_range);
-    pullAndUpdateDual(time + 2, g_key_range, grp, col_range, msg);
-  }
+    const int grp = call.fea_grp(0);
+    const Range<Key> block = call.key().to<Key>();
+    const SizeR cols = model_.find(grp, block);
 
-  void computeAndPushGradient(int time, Range<Key> g_key_range, int grp, SizeR col_range) {
-    SArray<Real> G(col_range.size(), 0), U(col_range.size(), 0);
-    {
-      Lock l(mu_);  // dual_ is shared with the pull callback (model executor thread)
-      busy_timer_.start();
-      if (!col_range.empty()) {
-        int nt = col_range.size() < 64 ? 1 : std::max(1, (int)FLAGS_num_threads);
-        parallelFor(nt, nt, [&](int t) {
-          SizeR thr = col_range.evenDivide(nt, t);
-          if (!thr.empty()) gradientOfColumns(grp, thr, G.data() - col_range.begin(), U.data() - col_range.begin());
-        });
-      }
-      busy_timer_.stop();
+    SArray<Real> G(cols.size(), 0), U(cols.size(), 0);
+    if (!cols.empty()) {
+      Lock l(mu_);  // dual_ is also written by the pull callback (model executor thread)
+      busy_.start();
+      const auto X = matrix(grp);
+      const CoordinateState& st = state_[grp];
+      const int threads = cols.size() < 64 ? 1 : std::max(1, (int)FLAGS_num_threads);
+      parallelFor(threads, threads, [&](int t) {
+        const SizeR part = cols.evenDivide(threads, t);
+        if (part.empty()) return;
+        Real* g = G.data() + (part.begin() - cols.begin());
+        Real* u = U.data() + (part.begin() - cols.begin());
+        if (X->binary())
+          DarlinMath::columnGradients<true>(*X, y_.data(), dual_.data(), st.active, st.delta.data(), part.begin(), part.end(), g, u);
+        else
+          DarlinMath::columnGradients<false>(*X, y_.data(), dual_.data(), st.active, st.delta.data(), part.begin(), part.end(), g, u);
+      });
+      busy_.stop();
     }
-    MessagePtr push(new Message(kServerGroup, time));
-    push->setKey(model_.key(grp).segment(col_range));
-    push->addValue({G, U});
-    push->task.mutable_key_range().from(g_key_range);
-    push->task.set_key_channel(grp);
-    push->addFilter(FilterConfigView::KEY_CACHING);
-    CHECK_EQ(time, model_.push(push));
-  }
-
-  // g_j = -sum_i y_i tau_i x_ij,  u_j = sum_i min(tau_i (1-tau_i) e^{|x_ij| delta_j}, 1/4) x_ij^2
-  void gradientOfColumns(int grp, SizeR cols, Real* G, Real* U) {
-    auto X = std::static_pointer_cast<SparseMatrix<uint32, Real>>(X_[grp]);
-    CHECK(X->colMajor());
-    const Bitmap& active = active_set_[grp];
-    const SArray<Real>& delta = delta_[grp];
-    const size_t* offset = X->offset().data();
-    const uint32* index = X->index().data();
-    const Real* value = X->value().data();
-    const bool binary = X->binary();
-    const Real* y = y_.data();
-    for (size_t j = cols.begin(); j < cols.end(); ++j) {
-      if (!active.test(j)) {
-        kkt_filter_.mark(G + j);
-        kkt_filter_.mark(U + j);
-        continue;
-      }
-      Real g = 0, u = 0;
-      const Real d = binary ? exp(delta[j]) : delta[j];
-      for (size_t o = offset[j]; o < offset[j + 1]; ++o) {
-        const uint32 i = index[o];
-        const Real tau = 1 / (1 + dual_[i]);
-        if (binary) {
-          g -= y[i] * tau;
-          u += std::min(tau * (1 - tau) * d, .25);
-        } else {
-          const Real v = value[o];
-          g -= y[i] * tau * v;
-          u += std::min(tau * (1 - tau) * exp(fabs(v) * d), .25) * v * v;
-        }
-      }
-      G[j] = g;
-      U[j] = u;
-    }
-  }
-
-  void pullAndUpdateDual(int time, Range<Key> g_key_range, int grp, SizeR col_range,
-                         const MessagePtr& msg) {
-    MessagePtr pull(new Message(kServerGroup, time, time - 1));
-    pull->setKey(model_.key(grp).segment(col_range));
-    pull->task.mutable_key_range().from(g_key_range);
-    pull->task.set_key_channel(grp);
-    pull->addFilter(FilterConfigView::KEY_CACHING);
-    pull->fin_handle = [this, time, grp, col_range, msg]() {
-      if (!col_range.empty()) {
-        auto data = model_.received(time);
-        CHECK_EQ(col_range, data.first);
-        CHECK_EQ(data.second.size(), (size_t)1);
-        updateDual(grp, col_range, data.second[0]);
-      }
-      // only now is the scheduler's UPDATE_MODEL task finished on this worker
-      port(msg->sender)->finishIncomingTask(msg->task.time());
-      sys_.reply(msg->sender, msg->task);
+    auto addressed = [&](int t, int wait) {
+      MessagePtr m(new Message(kServerGroup, t, wait));
+      m->setKey(model_.key(grp).segment(cols));
+      m->task.mutable_key_range().from(block);
+      m->task.set_key_channel(grp);
+      m->addFilter(FilterConfigView::KEY_CACHING);
+      return m;
     };
-    CHECK_EQ(time, model_.pull(pull));
+    MessagePtr push = addressed(time, Message::kInvalidTime);
+    push->addValue({model_.stage(G), model_.stage(U)});  // -device gpu: through peer memory
+    CHECK_EQ(time, model_.push(push));
+
+    const int tp = BcdClock::pull(time);
+    MessagePtr pull = addressed(tp, BcdClock::updated(time));
+    pull->fin_handle = [this, tp, grp, cols, task]() {
+      if (!cols.empty()) {
+        auto got = model_.receivedOnHost(tp);
+        CHECK_EQ(got.first, cols);
+        CHECK_EQ(got.second.size(), (size_t)1);
+        adoptWeights(grp, cols, got.second[0]);
+      }
+      port(task->sender)->finishIncomingTask(task->task.time());
+      sys_.reply(task->sender, task->task);
+    };
+    CHECK_EQ(tp, model_.pull(pull));
   }
 
-  void updateDual(int grp, SizeR col_range, SArray<Real> new_w) {
-    SArray<Real>& cur_w = model_.value(grp);
-    Bitmap& active = active_set_[grp];
-    SArray<Real>& delta = delta_[grp];
+  // ref darlin.h:429-502: a NaN weight means "the server filtered this coordinate"
+  void adoptWeights(int grp, SizeR cols, const SArray<Real>& fresh) {
+    CoordinateState& st = state_[grp];
+    SArray<Real>& w = model_.value(grp);
     const Real delta_max = bcd_conf_.delta_max_value();
-    SArray<Real> delta_w(new_w.size());
-    for (size_t i = 0; i < new_w.size(); ++i) {
-      const size_t j = col_range.begin() + i;
-      if (kkt_filter_.marked(new_w[i])) {
-        active.clear(j);
-        cur_w[j] = 0;
-        delta_w[i] = 0;
+    SArray<Real> dw(fresh.size(), 0);
+    for (size_t i = 0; i < fresh.size(); ++i) {
+      const size_t j = cols.begin() + i;
+      if (SparseFilter::marked(fresh[i])) {
+        st.active.clear(j);
+        w[j] = 0;
         continue;
       }
-      delta_w[i] = new_w[i] - cur_w[j];
-      delta[j] = newDelta(delta_max, delta_w[i]);
-      cur_w[j] = new_w[i];
+      dw[i] = fresh[i] - w[j];
+      st.delta[j] = DarlinMath::trustRegion(delta_max, dw[i]);
+      w[j] = fresh[i];
     }
-    auto X = std::static_pointer_cast<SparseMatrix<uint32, Real>>(X_[grp]);
-    CHECK(X && X->colMajor());
-    const size_t* offset = X->offset().data();
-    const uint32* index = X->index().data();
-    const Real* value = X->value().data();
-    const bool binary = X->binary();
-    const Real* y = y_.data();
+    const auto X = matrix(grp);
     Lock l(mu_);
-    busy_timer_.start();
-    int nt = std::max(1, (int)FLAGS_num_threads);
-    const size_t rows = X->rows();
-    parallelFor(nt, nt, [&](int t) {  // every thread owns a slice of the rows: no write conflicts
-      SizeR rr = SizeR(0, rows).evenDivide(nt, t);
-      for (size_t jj = 0; jj < col_range.size(); ++jj) {
-        const size_t j = col_range.begin() + jj;
-        const Real wd = delta_w[jj];
-        if (wd == 0 || !active.test(j)) continue;
-        for (size_t o = offset[j]; o < offset[j + 1]; ++o) {
-          const uint32 i = index[o];
-          if (!rr.contains(i)) continue;
-          dual_[i] *= binary ? exp(y[i] * wd) : exp(y[i] * wd * value[o]);
-        }
-      }
+    busy_.start();
+    const int threads = std::max(1, (int)FLAGS_num_threads);
+    const SizeR rows(0, X->rows());
+    parallelFor(threads, threads, [&](int t) {
+      const SizeR r = rows.evenDivide(threads, t);
+      if (X->binary())
+        DarlinMath::rescaleDual<true>(*X, y_.data(), st.active, dw.data(), cols.begin(), cols.end(), r.begin(), r.end(), dual_.data());
+      else
+        DarlinMath::rescaleDual<false>(*X, y_.data(), st.active, dw.data(), cols.begin(), cols.end(), r.begin(), r.end(), dual_.data());
     });
-    busy_timer_.stop();
+    busy_.stop();
   }
 
+  // ref darlin.h:504-511
   void evaluate(BCDProgress* prog) override {
     Lock l(mu_);
-    busy_timer_.start();
-    Real s = 0;
-    for (size_t i = 0; i < dual_.size(); ++i) s += log(1 + 1 / dual_[i]);
-    prog->set_objective(s);
-    prog->add_busy_time(busy_timer_.stop());
-    busy_timer_.restart();
+    busy_.start();
+    Real loss = 0;
+    for (Real d : dual_) loss += log(1 + 1 / d);
+    prog->set_objective(loss);
+    prog->add_busy_time(busy_.stop());
+    busy_.restart();
   }
 
-  Timer busy_timer_;
+ private:
+  std::shared_ptr<SparseMatrix<uint32, Real>> matrix(int grp) {
+    auto X = std::static_pointer_cast<SparseMatrix<uint32, Real>>(X_[grp]);
+    CHECK(X && X->colMajor()) << "group " << grp << " is not localized by column";
+    return X;
+  }
+  Config conf_;
+  std::unordered_map<int, CoordinateState> state_;
+  Timer busy_;
 };
 
 }  // namespace LM

@@ -9,9 +9,9 @@
 namespace PS {
 namespace LM {
 
-class ModelEvaluation : public App, public LinearMethod {
+class ModelEvaluation : public App {
  public:
-  ModelEvaluation(const string& name, const ConfigView& conf) : App(name), LinearMethod(conf) {}
+  ModelEvaluation(const string& name, const ConfigView& conf) : App(name), conf_(conf) {}
   virtual ~ModelEvaluation() { stopExecutor(); }
   void init() override {}
   void run() override {
@@ -65,6 +65,7 @@ class ModelEvaluation : public App, public LinearMethod {
   size_t numExamples() const { return num_ex_; }
 
  private:
+  Config conf_;
   double auc_ = 0, accuracy_ = 0;
   size_t num_ex_ = 0;
 };

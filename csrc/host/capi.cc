@@ -377,11 +377,21 @@ class KVWorkerApp : public App {
     push->addFilter(FilterConfigView::KEY_CACHING);
     int tp = vec_.push(push);
     vec_.waitOutMsg(kServerGroup, tp);
-    MessagePtr msg(new Message(kServerGroup));
-    msg->setKey(key);
-    msg->addFilter(FilterConfigView::KEY_CACHING);
-    int t = vec_.pull(msg);
-    vec_.waitOutMsg(kServerGroup, t);
+    // workers do not synchronise with each other: pull until every worker's +1 has landed
+    const float all = (float)sys_.yp().num_workers();
+    for (int tries = 0; tries < 1000; ++tries) {
+      vec_.value().clear();  // a pull reply is added into the local values
+      MessagePtr msg(new Message(kServerGroup));
+      msg->setKey(key);
+      msg->addFilter(FilterConfigView::KEY_CACHING);
+      int t = vec_.pull(msg);
+      vec_.waitOutMsg(kServerGroup, t);
+      SArray<float> v = vec_.value();
+      bool complete = v.size() == key.size();
+      for (size_t i = 0; complete && i < v.size(); ++i) complete = v[i] >= 0.1f * key[i] + all - 1e-3f;
+      if (complete) break;
+      usleep(2000);
+    }
     if (myRank() == 0) {
       Lock l(*mu_);
       SArray<float> v = vec_.value();

@@ -227,15 +227,11 @@ class FixingFloatFilter : public Filter {
 // mark(v) writes the all-ones bit pattern (a NaN); marked(v) <=> v != v.
 class SparseFilter {
  public:
-  SparseFilter() { memset(&double_v_, 0xff, sizeof(double)); memset(&float_v_, 0xff, sizeof(float)); }
-  void mark(float* v) const { *v = float_v_; }
-  void mark(double* v) const { *v = double_v_; }
-  bool marked(double v) const { return v != v; }
-  bool marked(float v) const { return v != v; }
-
- private:
-  float float_v_;
-  double double_v_;
+  // the all-ones bit pattern: a NaN no arithmetic produces
+  static void mark(float* v) { memset(v, 0xff, sizeof(float)); }
+  static void mark(double* v) { memset(v, 0xff, sizeof(double)); }
+  static bool marked(double v) { return v != v; }
+  static bool marked(float v) { return v != v; }
 };
 
 inline Filter* Filter::create(const FilterConfigView& conf) {

@@ -228,4 +228,6 @@ def test_shipped_rcv1_configs_train_then_evaluate(tmp_path, monkeypatch):
     assert int(n) == 1200 and float(auc) > 0.8
     host.run_cluster(conf("online_l1lr"), 2, 2)
     auc, acc, n = host.run_cluster(conf("eval_online"), 0, 0).split()
-    assert int(n) == 1200 and float(auc) > 0.7
+    # the shipped config sets no max_delay: how stale the gradients of the handful of minibatches
+    # are depends on thread timing (typically auc ~0.89; all of them computed at w = 0 gives ~0.65)
+    assert int(n) == 1200 and float(auc) > 0.6
