@@ -66,3 +66,42 @@ def test_traffic_goes_through_peer_memory():
     """With -traffic_statistics the van reports its bytes; in gpu mode the staged frames are counted too."""
     _, err = _run("kvops", 2, 2, "-device", "gpu", "-traffic_statistics")
     assert "Gbyte" in err
+
+
+def _darlin_table(err):
+    """rows of the per-pass table the scheduler prints: (iter, objective, |w|_0, #active)"""
+    rows = []
+    for l in err.splitlines():
+        p = l.split("|")
+        if len(p) >= 4 and p[0].strip().isdigit():
+            rows.append((int(p[0]), p[1].split()[0], int(p[2]), int(p[3].split()[1])))
+    return rows
+
+
+@pytest.mark.gpu
+def test_darlin_binary_with_model_shards_in_hbm(tmp_path):
+    """build/ps (the C++ scheduler / servers / workers) on a Darlin config: with -device gpu the
+    model shards are HBM columns and (G, U) / weight blocks travel through peer memory; the
+    objective table must be the one of the CPU run."""
+    from parameter_server_b200.utils.synthetic import make_rcv1_like, write_libsvm
+    os.makedirs(tmp_path / "train")
+    for p in range(4):
+        write_libsvm(make_rcv1_like(1500, 600, 20.0, seed=3, shard=p), str(tmp_path / "train" / f"part-{p}"))
+    tables = {}
+    for mode in ("cpu", "gpu"):
+        conf = tmp_path / f"{mode}.conf"
+        conf.write_text(f'''
+linear_method {{
+  training_data {{ format: TEXT text: LIBSVM file: "{tmp_path}/train/part.*" }}
+  model_output {{ format: TEXT file: "{tmp_path}/model_{mode}/m" }}
+  loss {{ type: LOGIT }}
+  penalty {{ type: L1 lambda: 0.5 }}
+  learning_rate {{ type: CONSTANT alpha: 1 }}
+  darlin {{ max_pass_of_data: 4 epsilon: 1e-7 feature_block_ratio: 0.5 max_block_delay: 0
+           random_feature_block_order: false local_cache {{ format: BIN file: "{tmp_path}/cache_{mode}/c" }} }}
+}}''')
+        _, err = _run("ps", 2, 2, "-app_file", str(conf), "-device", mode, timeout=300)
+        tables[mode] = _darlin_table(err)
+        assert len(tables[mode]) == 4, err[-2000:]
+    assert tables["gpu"] == tables["cpu"]
+    assert float(tables["gpu"][-1][1]) < float(tables["gpu"][0][1])
