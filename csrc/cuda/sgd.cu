@@ -20,6 +20,7 @@
 // The owner applies the landed gradients worker by worker in fixed order (k_sgd_server), which is
 // what the reference's server does with arriving pushes, and makes runs reproducible.
 #include "common.cuh"
+#include <cuda_fp8.h>
 #include "../../include/psb200.h"
 
 namespace psb {
@@ -200,14 +201,20 @@ k_sgd_worker_step(const __grid_constant__ SgdWorker W, uint64_t seq, uint32_t* b
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, o));
-        const float scale = mx > 0.f ? mx / 127.f : 1.f;
+        // int8: 127 levels per sign; fp8 e4m3: the block maximum maps to 448, the largest finite
+        // value, and small entries keep 3 mantissa bits instead of vanishing below one level
+        const float top = W.quant == 2 ? 448.f : 127.f;
+        const float scale = mx > 0.f ? mx / top : 1.f;
         if (lane == 0) d_scale[b] = scale;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           const int64_t i = b * kQuantBlock + k * 32 + lane;
           if (i < n) {
             d_slot[i] = (int32_t)W.col_slot[lo + i];
-            d_q[i] = (int8_t)__float2int_rn(v[k] / scale);
+            if (W.quant == 2)
+              d_q[i] = (int8_t)__nv_cvt_float_to_fp8(v[k] / scale, __NV_SATFINITE, __NV_E4M3);
+            else
+              d_q[i] = (int8_t)__float2int_rn(v[k] / scale);
           }
         }
       }
@@ -245,8 +252,16 @@ __device__ __forceinline__ void sgd_apply_worker(const SgdServer& S, int wkr, ui
   for (int64_t i = gt; i < n; i += nt) {
     const int32_t slot = __ldcg(S.land_slot + base + i);
     if (slot < 0) continue;
-    const float g = S.quant ? (float)__ldcg(S.land_q + base + i) * __ldcg(S.land_scale + sbase + i / kQuantBlock)
-                            : __ldcg(S.land_val + base + i);
+    float g;
+    if (S.quant == 0) {
+      g = __ldcg(S.land_val + base + i);
+    } else {
+      const int8_t code = __ldcg(S.land_q + base + i);
+      const float unit = S.quant == 2
+          ? __half2float(__half(__nv_cvt_fp8_to_halfraw((__nv_fp8_storage_t)code, __NV_E4M3)))
+          : (float)code;
+      g = unit * __ldcg(S.land_scale + sbase + i / kQuantBlock);
+    }
     const float w_old = S.w[slot];
     float w_new;
     if (S.algo == 0) {  // FTRL-proximal
@@ -256,15 +271,15 @@ __device__ __forceinline__ void sgd_apply_worker(const SgdServer& S, int wkr, ui
       const float z = S.z[slot] + g - sigma * w_old;
       S.z[slot] = z;
       S.n[slot] = sn_new;
-      const float eta = S.alpha / (sn_new + S.beta);
+      const float eta = S.lr_constant ? S.alpha : S.alpha / (sn_new + S.beta);
       w_new = prox_enet(-z * eta, eta, S.l1, S.l2);
     } else if (S.algo == 1) {  // AdaGrad
       const float ss = S.z[slot] + g * g;
       S.z[slot] = ss;
-      const float eta = S.alpha / (sqrtf(ss) + S.beta);
+      const float eta = S.lr_constant ? S.alpha : S.alpha / (sqrtf(ss) + S.beta);
       w_new = prox_enet(w_old - eta * g, eta, S.l1, S.l2);
     } else {  // SGD
-      const float eta = S.alpha / (S.sgd_t + S.beta);
+      const float eta = S.lr_constant ? S.alpha : S.alpha / (S.sgd_t + S.beta);
       w_new = prox_enet(w_old - eta * g, eta, S.l1, S.l2);
     }
     S.w[slot] = w_new;

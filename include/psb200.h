@@ -259,7 +259,7 @@ typedef struct psb_sgd_worker {
   int64_t land_cap;
   int32_t rank, n_workers, n_servers, depth;
   int32_t loss;    /* LossConfig::Type: 1 SQUARE, 2 LOGIT, 4 SQUARE_HINGE */
-  int32_t quant;   /* 0: fp32 push; 1: int8 with one fp32 scale per 128 values */
+  int32_t quant;   /* 0: fp32 push; 1: int8, 2: fp8 e4m3, both with one fp32 scale per 128 values */
 } psb_sgd_worker;
 
 typedef struct psb_sgd_server {
@@ -281,6 +281,8 @@ typedef struct psb_sgd_server {
   int32_t quant;
   float alpha, beta, l1, l2;
   float sgd_t;               /* sqrt(iteration) for the plain SGD step size */
+  int32_t lr_constant;       /* learning_rate.type CONSTANT: eta = alpha (ref learning_rate.h:15-22);
+                                0 = DECAY alpha / (x + beta) */
 } psb_sgd_server;
 
 /* table set-up and key resolution (K8a).  Capacities are powers of two. */

@@ -8,15 +8,25 @@ kernel (pull weights from the owners' tables in peer memory -> margins, loss, gr
 landed pushes in worker order and acknowledges.  `max_delay` = tau is honoured: a worker owns
 tau+1 landing regions per server and may run at most tau pushes ahead of the acknowledgements.
 
-The (owner, slot) resolution of a minibatch's unique keys is computed once and cached for the
-following data passes (the device successor of the KEY_CACHING filter).
+Two ways to feed it:
+  load(data) + train()      the whole data set resident in HBM; the (owner, slot) resolution of
+                            a minibatch is cached for the following passes up to `cache_bytes`
+                            (the device successor of the KEY_CACHING filter);
+  train_stream(source)      minibatches arrive from the host (the StreamReader of the reference,
+                            src/learner/sgd.h:104-157): a prefetch thread copies them from pinned
+                            memory (one async copy per array) and localises them on a side stream
+                            while the step kernels of earlier minibatches run; nothing is kept.
+The tail-feature filter is the reference's: one CountMin sketch per worker that lives across
+minibatches (insert the counts of a minibatch, keep the keys whose estimate exceeds the bound).
 """
 from __future__ import annotations
 
 import ctypes as C
 import math
 import os
+import queue
 import sys
+import threading
 import time
 from dataclasses import dataclass
 
@@ -53,7 +63,7 @@ class SgdServerStruct(C.Structure):
                 ("ack_out", P * MAX_PEERS), ("land_cap", C.c_int64), ("stats", P),
                 ("rank", C.c_int32), ("n_workers", C.c_int32), ("depth", C.c_int32),
                 ("algo", C.c_int32), ("quant", C.c_int32), ("alpha", C.c_float), ("beta", C.c_float),
-                ("l1", C.c_float), ("l2", C.c_float), ("sgd_t", C.c_float)]
+                ("l1", C.c_float), ("l2", C.c_float), ("sgd_t", C.c_float), ("lr_constant", C.c_int32)]
 
 
 @dataclass
@@ -68,8 +78,14 @@ class AsyncSGDConfig:
     beta: float = 1.0
     lambda_l1: float = 0.0
     lambda_l2: float = 0.0
+    lr_type: str = "DECAY"           # learning_rate.type: DECAY alpha/(x+beta) | CONSTANT alpha
     tail_feature_freq: int = 0
-    fixing_float_by_nbytes: int = 0  # != 0 -> int8 block-scaled push (K9)
+    countmin_n: int = 100_000_000    # cells / probes of the worker's tail-filter sketch (linear.proto:60-61)
+    countmin_k: int = 2
+    fixing_float_by_nbytes: int = 0  # != 0 -> block-scaled 8-bit push (K9), see push_format
+    push_format: str = "int8"        # int8 | fp8 (e4m3), one fp32 scale per 128 values
+    cache_bytes: int = 8 << 30       # resident mode: budget for cached localised minibatches
+    prefetch: int = 3                # streaming mode: localised minibatches kept ahead of the step
     table_capacity: int = 1 << 22    # slots per shard (power of two)
     report_every: int = 10           # minibatches between progress lines
     fused_server: bool = True        # one cooperative server launch per step instead of 1 + n_workers
@@ -84,12 +100,14 @@ class AsyncSGDConfig:
         c.algo = "FTRL" if algo == "FTRL" else ("ADAGRAD" if ada else "SGD")
         c.loss = g(conf_text, base + "loss.type") or "LOGIT"
         for name, typ in (("minibatch", int), ("num_data_pass", int), ("max_delay", int),
-                          ("tail_feature_freq", int), ("fixing_float_by_nbytes", int)):
+                          ("tail_feature_freq", int), ("fixing_float_by_nbytes", int),
+                          ("countmin_n", int), ("countmin_k", int)):
             v = g(conf_text, base + "async_sgd." + name)
             if v:
                 setattr(c, name, typ(float(v)))
         c.alpha = float(g(conf_text, base + "learning_rate.alpha") or 1)
         c.beta = float(g(conf_text, base + "learning_rate.beta") or 1)
+        c.lr_type = g(conf_text, base + "learning_rate.type") or "DECAY"
         ptype = g(conf_text, base + "penalty.type") or "L1"
         l0 = float(g(conf_text, base + "penalty.lambda[0]") or 0)
         l1 = float(g(conf_text, base + "penalty.lambda[1]") or 0)
@@ -139,20 +157,34 @@ class AsyncSGDEngine:
         self.seq = 0
         self.history = []   # (examples, loss, accuracy, auc)
         self._cache = {}
+        self._cache_used = 0
         self.launches = 0
+        self.h2d_bytes = 0
+        self.data = None
+        self.n_rows = 0
 
     # --------------------------------------------------------------------------------------------
     def load(self, data: SparseCSR, max_unique_per_minibatch: int | None = None) -> None:
-        cfg, dev, W = self.cfg, self.device, self.world
+        """Resident mode: the worker's rows live in HBM for all passes."""
+        dev = self.device
         self.data = data.to(dev)
         self.n_rows = data.n_rows
+        max_row = int((self.data.row_ptr[1:] - self.data.row_ptr[:-1]).max().item()) if self.n_rows else 1
+        cap = max_unique_per_minibatch or min(self.cfg.minibatch * max(max_row, 1), self.data.nnz + 1)
+        self.open(cap)
+        self.n_minibatches = (self.n_rows + self.cfg.minibatch - 1) // self.cfg.minibatch
+        # every rank runs the same number of steps (ranks with fewer rows send empty pushes)
+        self.steps_per_pass = int(max(self.comm.gather_obj(self.n_minibatches)))
+
+    def open(self, max_unique_per_minibatch: int) -> None:
+        """Allocate the shard (hash table + optimizer state), the landing rings and the flags.
+        `max_unique_per_minibatch`: upper bound of the distinct keys one minibatch sends to one
+        owner (the size of a ring region)."""
+        cfg, dev, W = self.cfg, self.device, self.world
         assert cfg.table_capacity & (cfg.table_capacity - 1) == 0
         self.depth = max(1, cfg.max_delay + 1)
-        mb_rows = cfg.minibatch
-        max_row = int((self.data.row_ptr[1:] - self.data.row_ptr[:-1]).max().item()) if self.n_rows else 1
-        land_cap = max_unique_per_minibatch or min(mb_rows * max(max_row, 1), self.data.nnz + 1)
         # the arena layout must be identical on every rank: take the largest request
-        land_cap = int(max(self.comm.gather_obj(int(land_cap))))
+        land_cap = int(max(self.comm.gather_obj(int(max_unique_per_minibatch))))
         land_cap = (land_cap + 127) // 128 * 128
         self.land_cap = land_cap
         nblk = land_cap // 128 + 1
@@ -195,6 +227,7 @@ class AsyncSGDEngine:
                                    dtype=torch.int64, device=dev)
         self.tab_keys_ptrs = (P * W)(*[A.peer_ptr(s, self.b_keys) for s in range(W)])
         self.tab_caps = (C.c_int64 * W)(*[cap] * W)
+        self.quant = 0 if not cfg.fixing_float_by_nbytes else {"int8": 1, "fp8": 2}[cfg.push_format]
         sv = SgdServerStruct()
         sv.w, sv.z, sv.n, sv.cap = self.b_w.ptr, self.b_z.ptr, self.b_n.ptr, cap
         sv.land_slot, sv.land_val, sv.land_q = self.b_lslot.ptr, self.b_lval.ptr, self.b_lq.ptr
@@ -203,43 +236,46 @@ class AsyncSGDEngine:
             sv.ack_out[w] = A.peer_ptr(w, self.b_ack, self.rank)
         sv.land_cap, sv.stats = land_cap, self.sstats.data_ptr()
         sv.rank, sv.n_workers, sv.depth = self.rank, W, D
-        sv.algo, sv.quant = ALGO[cfg.algo], int(cfg.fixing_float_by_nbytes != 0)
+        sv.algo, sv.quant = ALGO[cfg.algo], self.quant
         sv.alpha, sv.beta, sv.l1, sv.l2, sv.sgd_t = cfg.alpha, cfg.beta, cfg.lambda_l1, cfg.lambda_l2, 1.0
+        sv.lr_constant = int(cfg.lr_type.upper() == "CONSTANT")
         self.sv = sv
-        self.n_minibatches = (self.n_rows + mb_rows - 1) // mb_rows
-        nmb = self.comm.allreduce_sum([float(self.n_minibatches)], dev)
-        # every rank runs the same number of steps (ranks with fewer rows send empty pushes)
-        self.steps_per_pass = int(max(self.n_minibatches, math.ceil(nmb[0] / W)))
-        if W > 1:
-            g = self.comm.gather_obj(self.n_minibatches)
-            self.steps_per_pass = max(g)
+        # the worker's tail-feature sketch lives across minibatches and passes (ref sgd.h:137-147)
+        self.tail_sketch = None
+        if cfg.tail_feature_freq > 0:
+            from ..ops.evaluation import CountMin
+            self.tail_sketch = CountMin(min(cfg.countmin_n, 1 << 30), cfg.countmin_k, dev)
 
     # --------------------------------------------------------------------------------------------
     def _prepare(self, mb: int) -> _Minibatch:
-        """Localize minibatch `mb` (K10 + K11 + K15 + K8a); cached across data passes."""
+        """Resident mode: localise minibatch `mb` of the loaded data (cached across passes while
+        the budget lasts; never with a tail filter, whose answer changes as counts accumulate)."""
         if mb in self._cache:
             return self._cache[mb]
-        cfg, dev, d = self.cfg, self.device, self.data
-        trace = os.environ.get("PSB_SGD_TRACE")
-
-        def mark(what):
-            if trace:
-                torch.cuda.synchronize(dev)
-                print(f"[trace] rank {self.rank} mb {mb} seq {self.seq} {what} t={time.time() % 1000:.3f}",
-                      file=sys.stderr, flush=True)
-        mark("prepare begin (previous step drained)")
+        cfg, d = self.cfg, self.data
         a = min(mb * cfg.minibatch, self.n_rows)
         b = min(a + cfg.minibatch, self.n_rows)
         lo, hi = int(d.row_ptr[a].item()), int(d.row_ptr[b].item())
-        keys_nnz = d.keys[lo:hi].contiguous()
-        uniq, cnt = L.unique_count(keys_nnz) if hi > lo else (keys_nnz, None)
-        if cfg.tail_feature_freq > 0 and hi > lo:
-            uniq = uniq[cnt > cfg.tail_feature_freq].contiguous()
+        m = self._localize((d.row_ptr[a:b + 1] - lo).contiguous(), d.keys[lo:hi].contiguous(),
+                           d.vals[lo:hi].contiguous() if d.vals is not None else None, d.y[a:b].contiguous())
+        size = sum(t.numel() * t.element_size() for t in (m.row_ptr, m.col, m.y, m.keys, m.col_owner, m.col_slot)
+                   ) + (m.val.numel() * 4 if m.val is not None else 0)
+        if self.tail_sketch is None and self._cache_used + size <= cfg.cache_bytes:
+            self._cache[mb] = m
+            self._cache_used += size
+        return m
+
+    def _localize(self, row_ptr: torch.Tensor, keys_nnz: torch.Tensor, vals, y: torch.Tensor) -> _Minibatch:
+        """K10 + K13 + K11 + K15 + K8a on the current stream: unique keys and counts, tail filter,
+        remap to local columns, owner segments, slots in the owners' tables."""
+        cfg, dev = self.cfg, self.device
+        nnz, n_rows = keys_nnz.numel(), row_ptr.numel() - 1
+        uniq, cnt = L.unique_count(keys_nnz) if nnz else (keys_nnz, None)
+        if self.tail_sketch is not None and nnz:
+            self.tail_sketch.insert(uniq, cnt.clamp(max=255))
+            uniq = uniq[self.tail_sketch.query_gt(uniq, cfg.tail_feature_freq)].contiguous()
         n_cols = uniq.numel()
-        mark(f"unique done n_cols={n_cols}")
-        idx1 = L.lookup_sorted(uniq, keys_nnz) if hi > lo else torch.empty(0, dtype=torch.int32, device=dev)
-        row_ptr = (d.row_ptr[a:b + 1] - lo).contiguous()
-        vals = d.vals[lo:hi].contiguous() if d.vals is not None else None
+        idx1 = L.lookup_sorted(uniq, keys_nnz) if nnz else torch.empty(0, dtype=torch.int32, device=dev)
         rp, col, val = L.compact_csr(row_ptr, idx1, vals)
         # owners: the sorted unique keys split at the shard boundaries
         W = self.world
@@ -249,23 +285,20 @@ class AsyncSGDEngine:
             cut = [n_cols] * (W - 1)
         ob = [0] + cut + [n_cols]
         owner_begin = torch.tensor(ob, dtype=torch.int64, device=dev)
-        col_owner = torch.zeros(max(n_cols, 1), dtype=torch.int32, device=dev)
-        for s in range(W):
-            col_owner[ob[s]:ob[s + 1]] = s
+        col_owner = torch.repeat_interleave(torch.arange(W, dtype=torch.int32, device=dev),
+                                            owner_begin[1:] - owner_begin[:-1]) if n_cols else \
+            torch.zeros(1, dtype=torch.int32, device=dev)
         col_slot = torch.full((max(n_cols, 1),), -1, dtype=torch.int64, device=dev)
         if n_cols:
-            assert max(ob[s + 1] - ob[s] for s in range(W)) <= self.land_cap, "landing region too small"
+            assert max(ob[s + 1] - ob[s] for s in range(W)) <= self.land_cap, \
+                "landing region too small: raise max_unique_per_minibatch"
             check(self.lib.psb_kv_lookup_insert(ptr(uniq), n_cols, ptr(col_owner), self.tab_keys_ptrs,
                                                 self.tab_caps, W, ptr(col_slot), ptr(self.overflow),
                                                 current_stream()))
-        mark("lookup_insert done")
         self._new_minibatches = getattr(self, "_new_minibatches", 0) + 1
-        if self._new_minibatches % 8 == 0:
+        if self._new_minibatches % 64 == 0:
             self.check_table_load()
-        m = _Minibatch(rp, col, val, d.y[a:b].contiguous(), uniq, col_owner, col_slot, owner_begin,
-                       b - a, n_cols)
-        self._cache[mb] = m
-        return m
+        return _Minibatch(rp, col, val, y, uniq, col_owner, col_slot, owner_begin, n_rows, n_cols)
 
     def _worker_struct(self, m: _Minibatch):
         cfg, A, W, D = self.cfg, self.arena, self.world, self.depth
@@ -292,12 +325,13 @@ class AsyncSGDEngine:
         wk.ack = self.b_ack.ptr
         wk.land_cap = self.land_cap
         wk.rank, wk.n_workers, wk.n_servers, wk.depth = r, W, W, D
-        wk.loss, wk.quant = LOSS[cfg.loss], int(cfg.fixing_float_by_nbytes != 0)
+        wk.loss, wk.quant = LOSS[cfg.loss], self.quant
         return wk
 
-    def worker_step(self, mb: int):
-        """Worker half of a step: pull -> gradient -> push of minibatch `mb` (one launch)."""
-        m = self._prepare(mb)
+    def worker_step(self, mb):
+        """Worker half of a step: pull -> gradient -> push of a minibatch (one launch).  `mb` is
+        an index into the loaded data or an already localised minibatch."""
+        m = mb if isinstance(mb, _Minibatch) else self._prepare(mb)
         self.seq += 1
         wk = self._worker_struct(m)
         grid = max(1, min(self.grid, (max(m.n_rows, m.n_cols // 8) + 7) // 8))
@@ -340,7 +374,7 @@ class AsyncSGDEngine:
             raise RuntimeError(f"rank {self.rank}: device wait timed out: {what.get(code, code)} "
                                f"(rank {idx // 100}, peer {idx % 100}) wanted seq {want}, saw {seen}")
 
-    def step(self, mb: int):
+    def step(self, mb):
         """One minibatch: worker kernel, then this rank's server applies every worker's push."""
         m = self.worker_step(mb)
         self.server_step()
@@ -358,6 +392,45 @@ class AsyncSGDEngine:
                 if (i + 1) % cfg.report_every == 0 or i + 1 == self.steps_per_pass:
                     self._report(seen, time.time() - t0, m, verbose)
         return self.history
+
+    # --------------------------------------------------------------------------------------------
+    def empty_minibatch(self) -> _Minibatch:
+        """What a rank pushes when it has run out of data while others have not."""
+        dev = self.device
+        z64 = torch.zeros(1, dtype=torch.int64, device=dev)
+        return self._localize(z64, torch.empty(0, dtype=torch.int64, device=dev), None,
+                              torch.empty(0, dtype=torch.float32, device=dev))
+
+    def train_stream(self, source, steps: int, verbose: bool = False, on_step=None) -> int:
+        """Streaming mode.  `source` yields host minibatches (SparseCSR whose tensors are in
+        pinned memory); a prefetch thread uploads and localises them `cfg.prefetch` ahead on its
+        own stream.  Runs exactly `steps` steps (the same number on every rank; a rank whose
+        source ends early pushes empty minibatches).  Returns the examples consumed."""
+        feeder = _Prefetcher(self, source, self.cfg.prefetch)
+        feeder.start()
+        main = torch.cuda.current_stream(self.device)
+        seen = 0
+        t0 = time.time()
+        try:
+            for i in range(steps):
+                item = feeder.get()
+                if item is None:
+                    m = self.empty_minibatch()
+                else:
+                    m, ready = item
+                    main.wait_event(ready)
+                    for t in (m.row_ptr, m.col, m.val, m.y, m.keys, m.col_owner, m.col_slot, m.owner_begin):
+                        if t is not None:
+                            t.record_stream(main)  # allocated on the prefetch stream, read here
+                self.step(m)
+                seen += m.n_rows
+                if on_step is not None:
+                    on_step(i, m)
+                if verbose and ((i + 1) % self.cfg.report_every == 0 or i + 1 == steps):
+                    self._report(seen, time.time() - t0, m, verbose)
+        finally:
+            feeder.stop()
+        return seen
 
     def _report(self, seen, secs, m, verbose):
         st = self.wstats.cpu().tolist()
@@ -402,6 +475,72 @@ class AsyncSGDEngine:
         if hasattr(self, "arena"):
             torch.cuda.synchronize(self.device)
             self.arena.close()
+
+
+class _Prefetcher(threading.Thread):
+    """Host minibatch -> HBM -> localised, ahead of the step loop (the producer half of the
+    reference's MinibatchReader, src/learner/sgd.h:120-129, with the H2D copy in place of the text
+    parser's queue).  One cudaMemcpyAsync per array from pinned memory on a dedicated stream; the
+    host syncs of the localisation (sizes of the unique-key lists) block only this thread."""
+
+    def __init__(self, engine, source, depth: int):
+        super().__init__(daemon=True)
+        self.eng, self.source = engine, iter(source)
+        self.q = queue.Queue(maxsize=max(1, depth))
+        self.stream = torch.cuda.Stream(engine.device)
+        self._halt = threading.Event()
+        self._ended = False
+        self.error = None
+
+    def run(self):
+        eng, dev = self.eng, self.eng.device
+        try:
+            torch.cuda.set_device(dev)
+            with torch.cuda.stream(self.stream):
+                for host in self.source:
+                    if self._halt.is_set():
+                        return
+                    up = lambda t: None if t is None else t.to(dev, non_blocking=True)  # noqa: E731
+                    rp, keys, vals, y = up(host.row_ptr), up(host.keys), up(host.vals), up(host.y)
+                    eng.h2d_bytes += sum(t.numel() * t.element_size() for t in (rp, keys, vals, y) if t is not None)
+                    m = eng._localize(rp, keys, vals, y)
+                    ready = torch.cuda.Event()
+                    ready.record(self.stream)
+                    while not self._halt.is_set():
+                        try:
+                            self.q.put((m, ready), timeout=0.1)
+                            break
+                        except queue.Full:
+                            continue
+        except BaseException as e:  # noqa: BLE001 - surfaced by get()
+            self.error = e
+        finally:
+            while not self._halt.is_set():
+                try:
+                    self.q.put(None, timeout=0.1)
+                    break
+                except queue.Full:
+                    continue
+
+    def get(self):
+        """The next localised minibatch, or None once the source is exhausted (and from then on)."""
+        if self._ended:
+            return None
+        item = self.q.get()
+        if self.error is not None:
+            raise self.error
+        if item is None:
+            self._ended = True
+        return item
+
+    def stop(self):
+        self._halt.set()
+        while True:
+            try:
+                self.q.get_nowait()
+            except queue.Empty:
+                break
+        self.join(timeout=10)
 
 
 def _as_i64(u: int) -> int:

@@ -75,6 +75,7 @@ def _reference_sgd(shards, cfg, steps, world):
         return (z - l) / (1 + cfg.lambda_l2 * eta) if z > 0 else (z + l) / (1 + cfg.lambda_l2 * eta)
 
     f = np.float32
+    const_lr = cfg.lr_type == "CONSTANT"  # learning_rate.h:15-22: eta = alpha
     for step in range(steps):
         pushes = []
         tot_loss, tot_rows = 0.0, 0
@@ -107,26 +108,27 @@ def _reference_sgd(shards, cfg, steps, world):
                     n2 = f(math.sqrt(n * n + gi * gi))
                     z = f(z + gi - (n2 - n) / f(cfg.alpha) * w)
                     n = n2
-                    eta = f(cfg.alpha) / (n + f(cfg.beta))
+                    eta = f(cfg.alpha) if const_lr else f(cfg.alpha) / (n + f(cfg.beta))
                     w = f(prox(-z * eta, eta))
                 elif cfg.algo == "ADAGRAD":
                     z = f(z + gi * gi)
-                    eta = f(cfg.alpha) / (f(math.sqrt(z)) + f(cfg.beta))
+                    eta = f(cfg.alpha) if const_lr else f(cfg.alpha) / (f(math.sqrt(z)) + f(cfg.beta))
                     w = f(prox(w - eta * gi, eta))
                 else:
-                    eta = f(cfg.alpha) / (f(math.sqrt(step + 1)) + f(cfg.beta))
+                    eta = f(cfg.alpha) if const_lr else f(cfg.alpha) / (f(math.sqrt(step + 1)) + f(cfg.beta))
                     w = f(prox(w - eta * gi, eta))
                 state[k] = (w, z, n)
     return losses, {k: v[0] for k, v in state.items() if v[0] != 0}
 
 
-def _run_engines(world, algo, quant=0, tau=0, steps=12):
+def _run_engines(world, algo, quant=0, tau=0, steps=12, lr_type="DECAY", alpha=0.5, push_format="int8"):
     from parameter_server_b200.models.async_sgd import AsyncSGDConfig, AsyncSGDEngine
     from parameter_server_b200.parallel.comm import run_threads
     from parameter_server_b200.utils.synthetic import make_rcv1_like
     dev = torch.device("cuda:0")
-    cfg = AsyncSGDConfig(algo=algo, minibatch=256, alpha=0.5, beta=1.0, lambda_l1=0.02, lambda_l2=0.01,
-                         max_delay=tau, fixing_float_by_nbytes=quant, table_capacity=1 << 14)
+    cfg = AsyncSGDConfig(algo=algo, minibatch=256, alpha=alpha, beta=1.0, lambda_l1=0.02, lambda_l2=0.01,
+                         max_delay=tau, fixing_float_by_nbytes=quant, table_capacity=1 << 14, lr_type=lr_type,
+                         push_format=push_format)
     shards = [make_rcv1_like(steps * 256, 3000, 24.0, seed=4, shard=r, device=dev) for r in range(world)]
     # spread the keys over the whole uint64 range so that every shard owns some
     for s in shards:
@@ -181,3 +183,85 @@ def test_sgd_int8_push_and_bounded_delay_ring():
     _, _, q8, _ = _run_engines(2, "FTRL", quant=1, tau=2)
     # block-scaled int8 gradients track the fp32 run closely and still learn
     assert q8[-1] < q8[0] and abs(q8[-1] - exact[-1]) < 0.03
+
+
+@pytest.mark.parametrize("algo", ["FTRL", "ADAGRAD", "SGD"])
+def test_sgd_constant_learning_rate(algo):
+    """learning_rate { type: CONSTANT }: eta = alpha in all three server updates (learning_rate.h:15-22)"""
+    cfg, shards, losses, model = _run_engines(1, algo, lr_type="CONSTANT", alpha=0.05)
+    ref_losses, ref_model = _reference_sgd(shards, cfg, len(losses), 1)
+    assert np.allclose(losses, ref_losses, rtol=2e-4, atol=1e-6)
+    ref_model = {k & 0xFFFFFFFFFFFFFFFF: v for k, v in ref_model.items()}
+    assert set(model) == set(ref_model)
+    a = np.array([model[k] for k in sorted(model)])
+    b = np.array([ref_model[k] for k in sorted(model)])
+    assert np.allclose(a, b, rtol=5e-3, atol=2e-5)
+    # and it is a different trajectory from DECAY with the same alpha
+    _, _, decay, _ = _run_engines(1, algo, lr_type="DECAY", alpha=0.05)
+    assert not np.allclose(losses[2:], decay[2:], rtol=1e-3)
+
+
+def test_sgd_fp8_push_tracks_fp32():
+    _, _, exact, _ = _run_engines(2, "FTRL", quant=0, tau=0)
+    _, _, q8, _ = _run_engines(2, "FTRL", quant=1, tau=0, push_format="fp8")
+    assert q8[-1] < q8[0] and abs(q8[-1] - exact[-1]) < 0.03
+
+
+def test_sgd_tail_filter_is_the_persistent_host_sketch():
+    """tail_feature_freq: keys are kept once their CUMULATIVE count over the minibatches seen so far
+    exceeds the bound (one CountMin per worker, src/learner/sgd.h:137-147) - checked against the
+    host sketch fed with the same sequence."""
+    from parameter_server_b200.models.async_sgd import AsyncSGDConfig, AsyncSGDEngine
+    from parameter_server_b200.runtime import host
+    from parameter_server_b200.utils.synthetic import make_rcv1_like
+    dev = torch.device("cuda:0")
+    cfg = AsyncSGDConfig(minibatch=200, tail_feature_freq=2, countmin_n=50000, countmin_k=2, table_capacity=1 << 14)
+    data = make_rcv1_like(1000, 2000, 10.0, seed=8, device=dev)
+    eng = AsyncSGDEngine(cfg, None, dev)
+    eng.load(data)
+    seen_k, seen_c = [], []
+    kept_any_late = False
+    for mb in range(5):
+        m = eng._prepare(mb)
+        a, b = mb * 200, (mb + 1) * 200
+        lo, hi = int(data.row_ptr[a]), int(data.row_ptr[b])
+        uniq, cnt = np.unique(data.keys[lo:hi].cpu().numpy().view(np.uint64), return_counts=True)
+        seen_k.append(uniq); seen_c.append(np.minimum(cnt, 255).astype(np.uint8))
+        keep, _ = host.countmin_filter(np.concatenate(seen_k), np.concatenate(seen_c), n=eng.tail_sketch.n, k=2, freq=2)
+        want = uniq[keep[-uniq.size:]]
+        assert np.array_equal(m.keys.cpu().numpy().view(np.uint64), want), mb
+        # a key that shows up once per minibatch is dropped at first and kept later
+        kept_any_late |= mb >= 2 and bool(np.any(cnt[keep[-uniq.size:]] == 1))
+    assert kept_any_late
+    eng.close()
+
+
+def test_sgd_streaming_equals_resident():
+    """train_stream (pinned host minibatches, prefetch thread, H2D + localisation on a side stream)
+    walks the same trajectory as the resident engine on the same minibatches."""
+    from parameter_server_b200.models.async_sgd import AsyncSGDConfig, AsyncSGDEngine
+    from parameter_server_b200.utils.synthetic import SparseCSR, make_rcv1_like
+    dev = torch.device("cuda:0")
+    data = make_rcv1_like(8 * 256, 3000, 24.0, seed=4, device="cpu")
+    cfg = AsyncSGDConfig(algo="FTRL", minibatch=256, alpha=0.5, lambda_l1=0.02, table_capacity=1 << 14)
+
+    def host_batches():
+        for a in range(0, data.n_rows, 256):
+            lo, hi = int(data.row_ptr[a]), int(data.row_ptr[a + 256])
+            yield SparseCSR((data.row_ptr[a:a + 257] - lo).pin_memory(), data.keys[lo:hi].pin_memory(),
+                            data.vals[lo:hi].pin_memory(), data.y[a:a + 256].pin_memory(), data.n_features)
+
+    res = AsyncSGDEngine(cfg, None, dev)
+    res.load(data)
+    for i in range(8):
+        res.step(i)
+    k0, w0 = res.shard_model()
+    loss0 = res.wstats.cpu().tolist()[0]
+    res.close()
+    st = AsyncSGDEngine(cfg, None, dev)
+    st.open(256 * 64)
+    assert st.train_stream(host_batches(), 10) == 8 * 256   # two steps past the end push nothing
+    k1, w1 = st.shard_model()
+    assert st.h2d_bytes > 0 and torch.equal(k0, k1) and torch.allclose(w0, w1, rtol=1e-6, atol=1e-7)
+    assert st.wstats.cpu().tolist()[0] == pytest.approx(loss0, rel=1e-6)
+    st.close()
