@@ -204,6 +204,8 @@ def main():
                        "first_pass_examples_per_s": ex_pass / (first_ms / 1e3),
                        "steady_examples_per_s": ex_pass / (steady_ms / 1e3) if args.passes > 1 else None,
                        "per_pass": per_pass, "generate_s": t_gen,
+                       "rank0_prefetch_busy_s": eng.prefetch_busy_s, "rank0_step_loop_waited_s": eng.feed_wait_s,
+                       "host_cpus": os.cpu_count(),
                        "timing": "CUDA events from the first minibatch of pass 0 (nothing cached or warmed), max over ranks"},
             "e2e": {"value": tot[0].item() / (wall_ms / 1e3), "unit": "examples/s",
                     "h2d_bytes_per_step": eng.h2d_bytes / max(steps * args.passes, 1), "d2h_bytes_per_step": 32.0 / steps,

@@ -45,6 +45,8 @@ def main():
     ap.add_argument("--density", type=float, default=0.5)
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--nccl", action="store_true", help="also time the NCCL all-to-all variant")
+    ap.add_argument("--tcp", action="store_true", help="also time the host TCP van on the same payload (rank 0)")
+    ap.add_argument("--check-up-to", type=float, default=2e7, help="verify the final state for sizes up to this")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -74,11 +76,46 @@ def main():
 
         t_push = timed(lambda: kv.push(h, vals), a.iters, sync)
         t_pull = timed(lambda: kv.pull(h, out), a.iters, sync)
-        # correctness of the last state: every push added vals; compare one pull against the owner arrays
-        t_bpush = timed(lambda: kv.push_bulk(h, vals), a.iters, sync)
+        # bulk push, zero copy: the application writes its values into the registered staging view
+        # (as one does with a registered NCCL buffer); bulk_push_copy_ms includes a D2D copy into it
+        stage = kv.push_buffer(h)
+        stage.copy_(vals)
+        t_bpush = timed(lambda: kv.push_bulk(h, stage), a.iters, sync)
+        t_bpush_copy = timed(lambda: kv.push_bulk(h, vals), a.iters, sync)
         t_bpull = timed(lambda: kv.pull_bulk(h), a.iters, sync)
         rec = {"n_keys": n, "push_ms": t_push, "pull_ms": t_pull, "bulk_push_ms": t_bpush,
-               "bulk_pull_ms": t_bpull}
+               "bulk_push_copy_ms": t_bpush_copy, "bulk_pull_ms": t_bpull}
+        # correctness of the final state: every rank pushed `vals` at its own key selection
+        # 3 * (iters + 3) times (direct, bulk, bulk with copy); a bulk pull must return exactly that sum
+        if n <= a.check_up_to:
+            sync()
+            n_push = 3 * (a.iters + 3)
+            want = torch.zeros(n, dtype=torch.float64, device=dev)
+            for r in range(world):
+                if r == rank:
+                    want += vals.double()
+                    continue
+                gr = torch.Generator(device=dev).manual_seed(100 + r)
+                other = torch.randperm(n_dict, generator=gr, device=dev)[:n].sort().values
+                pos = torch.searchsorted(other, sel).clamp_(max=n - 1)
+                hit = other[pos] == sel
+                want += torch.where(hit, vals[pos].double(), torch.zeros((), dtype=torch.float64, device=dev))
+                del other, pos, hit
+            got = kv.pull_bulk(h).double()
+            err = ((got - n_push * want).abs() / (1 + (n_push * want).abs())).max().item()
+            direct = ((kv.pull(h, out).double() - n_push * want).abs() / (1 + (n_push * want).abs())).max().item()
+            rec["max_rel_error"] = max(err, direct)
+            rec["correct"] = bool(max(err, direct) < 1e-4)
+            assert rec["correct"], rec
+        if a.tcp and rank == 0 and n <= 10_000_000:
+            # the CPU plumbing path: the same payload (keys + values) through the framed-TCP van
+            # between two nodes on this host, 4 hops (ref van_test.cc ring)
+            import time
+            from parameter_server_b200.runtime import host
+            t0 = time.perf_counter()
+            host.van_ring(2, True, 21000 + (os.getpid() + len(rows) * 7) % 9000, n)
+            rec["tcp_van_ms_per_hop"] = (time.perf_counter() - t0) * 1e3 / 4
+            rec["tcp_van_gbs"] = n * 12 / (rec["tcp_van_ms_per_hop"] * 1e-3) / 1e9
         if a.nccl and world > 1:
             # NCCL variant: values sorted by owner -> all_to_all_single -> local index_add / gather back
             counts = torch.bincount(h.owner[:n].long(), minlength=world)
@@ -109,6 +146,7 @@ def main():
             rec[k] = v
         gbs = lambda ms: n * 4 / (ms * 1e-3) / 1e9  # noqa: E731
         rec.update(bulk_push_gbs=gbs(rec["bulk_push_ms"]), bulk_pull_gbs=gbs(rec["bulk_pull_ms"]),
+                   bulk_push_copy_gbs=gbs(rec["bulk_push_copy_ms"]),
                    bulk_push_frac_of_770=gbs(rec["bulk_push_ms"]) / 770,
                    bulk_pull_frac_of_770=gbs(rec["bulk_pull_ms"]) / 770)
         rec.update(push_gbs=gbs(rec["push_ms"]), pull_gbs=gbs(rec["pull_ms"]),

@@ -220,6 +220,156 @@ __global__ void k_kv_wait_flags(const uint64_t* flags, int n, uint64_t seq) {
 
 }  // namespace psb
 
+// ---------------------------------------------------------------------------------------------
+// Bulk path, second generation: receiver-driven push.
+//
+// A worker leaves its values (sorted by owner) in a staging buffer of its OWN arena; after a rank
+// barrier every owner runs ONE cooperative kernel that walks the workers in a staggered order
+// (rank, rank+1, ...: no two owners read the same worker at the same time, so no egress link is
+// oversubscribed), loads that worker's segment straight from peer memory with 128-bit loads and
+// adds it into its shard at the cached 32-bit slots.  The payload crosses NVLink once and is
+// never written to or re-read from a landing region: per key the owner moves 4 B over the link,
+// 4 B of slot and one 8-byte read-modify-write - against 20 B with a landing region.  A grid
+// barrier separates two workers (their segments may hit the same slot), which also makes the
+// sum order fixed: run-to-run deterministic.
+// ---------------------------------------------------------------------------------------------
+namespace psb {
+
+struct BulkPullApply {
+  float* val;
+  const float* src[PSB_MAX_PEERS];     // worker w's staging, already offset to its segment for me
+  const int32_t* slots[PSB_MAX_PEERS]; // slots of that segment in my shard
+  int64_t count[PSB_MAX_PEERS];
+  int32_t n_workers, rank;
+};
+
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_peer_f1(const float* p) {
+  float v;
+  asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(256) k_kv_bulk_pull_apply(const __grid_constant__ BulkPullApply B, uint32_t* bar) {
+  const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nt = (int64_t)gridDim.x * blockDim.x;
+  for (int k = 0; k < B.n_workers; ++k) {
+    const int w = (B.rank + k) % B.n_workers;
+    const float* src = B.src[w];
+    const int32_t* sl = B.slots[w];
+    const int64_t n = B.count[w];
+    // scalar head up to the first 16-byte boundary of the peer segment, then 4 values per load
+    int64_t head = ((16 - ((uintptr_t)src & 15)) & 15) / 4;
+    if (head > n) head = n;
+    for (int64_t i = gt; i < head; i += nt) B.val[sl[i]] += ld_peer_f1(src + i);
+    const int64_t n4 = (n - head) / 4;
+    for (int64_t q = gt; q < n4; q += nt) {
+      const int64_t i = head + 4 * q;
+      const float4 v = ld_peer_f4(src + i);
+      const int32_t s0 = sl[i], s1 = sl[i + 1], s2 = sl[i + 2], s3 = sl[i + 3];
+      B.val[s0] += v.x; B.val[s1] += v.y; B.val[s2] += v.z; B.val[s3] += v.w;  // slots of one worker are distinct
+    }
+    for (int64_t i = head + 4 * n4 + gt; i < n; i += nt) B.val[sl[i]] += ld_peer_f1(src + i);
+    grid_arrive(bar);
+    if (k + 1 < B.n_workers) grid_wait(bar, (uint32_t)(k + 1) * gridDim.x);
+  }
+  if (blockIdx.x == 0) {
+    grid_wait(bar, (uint32_t)B.n_workers * gridDim.x);
+    if (threadIdx.x == 0) *bar = 0;
+  }
+}
+
+// owner -> workers: gather my values at worker w's slots and store them contiguously into w's
+// landing buffer (128-bit peer stores), workers in staggered order, then one flag per worker
+struct BulkGather32 {
+  const float* val;
+  const int32_t* slots[PSB_MAX_PEERS];
+  int64_t count[PSB_MAX_PEERS];
+  float* dst[PSB_MAX_PEERS];            // on worker w: where this owner's segment goes (16-byte aligned)
+  uint64_t* flag[PSB_MAX_PEERS];        // on worker w: &flag[rank]
+  uint32_t* done_ctr;
+  int32_t n_workers, rank;
+};
+
+__global__ void __launch_bounds__(256) k_kv_bulk_gather_send32(const __grid_constant__ BulkGather32 B, uint64_t seq) {
+  const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nt = (int64_t)gridDim.x * blockDim.x;
+  for (int k = 0; k < B.n_workers; ++k) {
+    const int w = (B.rank + k) % B.n_workers;
+    const int32_t* sl = B.slots[w];
+    float* dst = B.dst[w];
+    const int64_t n = B.count[w], n4 = n / 4;
+    for (int64_t q = gt; q < n4; q += nt) {
+      const int4 s4 = *reinterpret_cast<const int4*>(sl + 4 * q);
+      float4 v;
+      v.x = B.val[s4.x]; v.y = B.val[s4.y]; v.z = B.val[s4.z]; v.w = B.val[s4.w];
+      *reinterpret_cast<float4*>(dst + 4 * q) = v;
+    }
+    for (int64_t i = 4 * n4 + gt; i < n; i += nt) dst[i] = B.val[sl[i]];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    if (atomicAdd(B.done_ctr, 1u) == gridDim.x - 1) {
+      *B.done_ctr = 0;
+      __threadfence_system();
+      for (int w = 0; w < B.n_workers; ++w) st_release_sys(B.flag[w], seq);
+    }
+  }
+}
+
+}  // namespace psb
+
+// ONE cooperative launch: every worker's segment is read from peer memory and added into `val`.
+// src_host[w]: this process' mapping of worker w's staging, offset to its segment for this owner;
+// slots_host[w]: device array of int32 slots (16-byte aligned); bar: zeroed uint32.  The caller
+// guarantees (rank barrier) that every worker's staging is complete before the launch.
+PSB_API int psb_kv_bulk_pull_apply(float* val, const float* const* src_host, const int32_t* const* slots_host,
+                                   const int64_t* count_host, int32_t n_workers, int32_t rank, uint32_t* bar,
+                                   void* stream) {
+  PSB_REQUIRE(n_workers >= 1 && n_workers <= PSB_MAX_PEERS, "psb_kv_bulk_pull_apply: n_workers=%d", n_workers);
+  BulkPullApply B;
+  B.val = val;
+  int64_t most = 0;
+  for (int w = 0; w < n_workers; ++w) {
+    B.src[w] = src_host[w]; B.slots[w] = slots_host[w]; B.count[w] = count_host[w];
+    most = count_host[w] > most ? count_host[w] : most;
+  }
+  B.n_workers = n_workers;
+  B.rank = rank;
+  int per_sm = 0;
+  PSB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_kv_bulk_pull_apply, 256, 0));
+  int grid = per_sm * sm_count();
+  const int64_t want = (most / 4 + 255) / 256 + 1;
+  if (want < grid) grid = (int)want;
+  void* args[] = {(void*)&B, (void*)&bar};
+  PSB_CUDA(cudaLaunchCooperativeKernel((const void*)k_kv_bulk_pull_apply, dim3(grid), dim3(256), args, 0,
+                                       (cudaStream_t)stream));
+  return 0;
+}
+
+PSB_API int psb_kv_bulk_gather_send32(const float* val, const int32_t* const* slots_host, const int64_t* count_host,
+                                      float* const* dst_host, uint64_t* const* flag_host, int32_t n_workers,
+                                      int32_t rank, uint64_t seq, uint32_t* done_ctr, void* stream) {
+  PSB_REQUIRE(n_workers >= 1 && n_workers <= PSB_MAX_PEERS, "psb_kv_bulk_gather_send32: n_workers=%d", n_workers);
+  BulkGather32 B;
+  B.val = val;
+  int64_t total = 0;
+  for (int w = 0; w < n_workers; ++w) {
+    B.slots[w] = slots_host[w]; B.count[w] = count_host[w]; B.dst[w] = dst_host[w]; B.flag[w] = flag_host[w];
+    total += count_host[w];
+  }
+  B.done_ctr = done_ctr;
+  B.n_workers = n_workers;
+  B.rank = rank;
+  k_kv_bulk_gather_send32<<<grid_for(total / 4 + 1), 256, 0, (cudaStream_t)stream>>>(B, seq);
+  PSB_LAUNCH_CHECK();
+  return 0;
+}
+
 PSB_API int psb_kv_bulk_send(const float* src, const int64_t* seg_begin_host, float* const* dst_host,
                              uint64_t* const* flag_host, int32_t n_servers, uint64_t seq,
                              uint32_t* done_ctr, void* stream) {

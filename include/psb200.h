@@ -371,6 +371,16 @@ int psb_kv_bulk_gather_send(const float* val, const int64_t* const* slots_host, 
                             float* const* dst_host, uint64_t* const* flag_host, int32_t n_workers,
                             uint64_t seq, uint32_t* done_ctr, void* stream);
 int psb_kv_wait_flags(const uint64_t* flags, int32_t n, uint64_t seq, void* stream);
+/* receiver-driven bulk push: ONE cooperative launch per owner reads every worker's segment from that
+ * worker's staging buffer in peer memory (128-bit loads, workers in a staggered order, a grid barrier
+ * between two workers: deterministic) and adds it into `val` at 32-bit slots; bar: zeroed uint32 */
+int psb_kv_bulk_pull_apply(float* val, const float* const* src_host, const int32_t* const* slots_host,
+                           const int64_t* count_host, int32_t n_workers, int32_t rank, uint32_t* bar,
+                           void* stream);
+/* bulk pull with 32-bit slots, 128-bit peer stores and staggered worker order */
+int psb_kv_bulk_gather_send32(const float* val, const int32_t* const* slots_host, const int64_t* count_host,
+                              float* const* dst_host, uint64_t* const* flag_host, int32_t n_workers,
+                              int32_t rank, uint64_t seq, uint32_t* done_ctr, void* stream);
 
 
 /* ------------------------------------------------------------------------- *

@@ -160,6 +160,8 @@ class AsyncSGDEngine:
         self._cache_used = 0
         self.launches = 0
         self.h2d_bytes = 0
+        self.prefetch_busy_s = 0.0   # streaming: wall time the prefetch thread spent localising
+        self.feed_wait_s = 0.0       # streaming: wall time the step loop waited for the prefetcher
         self.data = None
         self.n_rows = 0
 
@@ -413,7 +415,9 @@ class AsyncSGDEngine:
         t0 = time.time()
         try:
             for i in range(steps):
+                t_q = time.perf_counter()
                 item = feeder.get()
+                self.feed_wait_s += time.perf_counter() - t_q
                 if item is None:
                     m = self.empty_minibatch()
                 else:
@@ -503,7 +507,9 @@ class _Prefetcher(threading.Thread):
                     up = lambda t: None if t is None else t.to(dev, non_blocking=True)  # noqa: E731
                     rp, keys, vals, y = up(host.row_ptr), up(host.keys), up(host.vals), up(host.y)
                     eng.h2d_bytes += sum(t.numel() * t.element_size() for t in (rp, keys, vals, y) if t is not None)
+                    t_loc = time.perf_counter()
                     m = eng._localize(rp, keys, vals, y)
+                    eng.prefetch_busy_s += time.perf_counter() - t_loc
                     ready = torch.cuda.Event()
                     ready.record(self.stream)
                     while not self._halt.is_set():

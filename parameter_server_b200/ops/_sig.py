@@ -34,6 +34,7 @@ CUDA_SIGS = {
     "psb_kv_route_dense": "pqpippp", "psb_kv_push_add_f32": "pppqpip", "psb_kv_pull_f32": "pppqpip",
     "psb_kv_bulk_send": "ppppiQpp", "psb_kv_bulk_apply_add": "pppqpQp",
     "psb_kv_bulk_gather_send": "pppppiQpp", "psb_kv_wait_flags": "piQp",
+    "psb_kv_bulk_pull_apply": "ppppiipp", "psb_kv_bulk_gather_send32": "pppppiiQpp",
     # darlin.cu
     "psb_darlin_pass_begin": "pppp", "psb_darlin_grad_push": "pppiiip",
     "psb_darlin_server_update": "pppiiip", "psb_darlin_pull_update": "pppiiip",

@@ -32,10 +32,11 @@ class KVHandle:
     slot: torch.Tensor
     n: int
     signature: int
-    # bulk path (register(..., bulk=True)): owner segments of my keys and, as an owner, the slot
-    # lists every worker will send values for
+    # bulk path (register(..., bulk=True)): owner segments of my keys and, as an owner, the (32-bit)
+    # slot lists of every worker's segment for me and where that segment starts in its staging
     seg_begin: list | None = None
     slots_from: list | None = None
+    src_off_from: list | None = None
 
 
 class DeviceKVVector:
@@ -62,16 +63,18 @@ class DeviceKVVector:
         self.shard_begin = torch.tensor(begins, dtype=torch.int64, device=self.device)
         self.shard_len = [begins[s + 1] - begins[s] for s in range(W)]
         cap = (max(max(self.shard_len), 1) + 3) // 4 * 4
-        # bulk path: per (owner, worker) landing regions for pushes and per (worker, owner) for pulls
+        # bulk path: this rank's push staging (values sorted by owner, read by the owners over
+        # NVLink) and per (worker, owner) landing regions for pulls
         self.bulk_cap = (int(bulk_capacity) + 3) // 4 * 4
         self.arena = self.comm.make_arena(cap * 4 + 2 * W * self.bulk_cap * 4 + 3 * W * 8 + 8192, self.device)
         self.b_val = self.arena.alloc("val", cap, torch.float32)
         self.b_bar = self.arena.alloc("bar", W, torch.int64)
-        self.b_land = self.arena.alloc("land_push", W * self.bulk_cap, torch.float32)
+        self.b_land = self.arena.alloc("push_staging", W * self.bulk_cap, torch.float32)
         self.b_pull = self.arena.alloc("land_pull", W * self.bulk_cap, torch.float32)
         self.b_pflag = self.arena.alloc("push_flag", W, torch.int64)
         self.b_gflag = self.arena.alloc("pull_flag", W, torch.int64)
         self.ctr = torch.zeros(4, dtype=torch.int32, device=self.device)
+        self.apply_bar = torch.zeros(4, dtype=torch.int32, device=self.device)
         self._seq = 0
         self.peers = (C.c_void_p * W)(*[self.arena.peer_ptr(s, self.b_val) for s in range(W)])
         self.bar_peers = (C.c_void_p * W)(*[self.arena.peer_ptr(s, self.b_bar) for s in range(W)])
@@ -99,6 +102,7 @@ class DeviceKVVector:
                                           ptr(slot), current_stream()))
         assert n == 0 or int(slot[:n].min().item()) >= 0, "keys outside the dictionary"
         h = KVHandle(keys, owner, slot, n, L.key_signature(keys) if n else 0)
+        assert max(self.shard_len) < 2 ** 31, "bulk slots are 32 bit"
         if bulk:  # collective: every rank registers its key list at the same time
             W = self.world
             counts = torch.bincount(owner[:n].long(), minlength=W).tolist() if n else [0] * W
@@ -108,7 +112,9 @@ class DeviceKVVector:
             assert max(counts) <= self.bulk_cap, "bulk_capacity too small for this key list"
             h.seg_begin = seg
             # the slot lists travel once (key caching); afterwards only values move
-            h.slots_from = self.comm.alltoall_var([slot[seg[s]:seg[s + 1]].contiguous() for s in range(W)])
+            h.slots_from = [t.to(torch.int32).contiguous() for t in
+                            self.comm.alltoall_var([slot[seg[s]:seg[s + 1]].contiguous() for s in range(W)])]
+            h.src_off_from = [sb[self.rank] for sb in self.comm.gather_obj(seg)]
         return h
 
     def push(self, h: KVHandle, values: torch.Tensor) -> None:
@@ -124,27 +130,33 @@ class DeviceKVVector:
         return out[:h.n]
 
     # ---- bulk path (collective calls: every rank pushes / pulls its handle) ----------------------
+    def push_buffer(self, h: KVHandle) -> torch.Tensor:
+        """The staging view to fill for a zero-copy push_bulk (values in key order); valid until the
+        next collective call."""
+        return self.b_land.tensor[:h.n]
+
     def push_bulk(self, h: KVHandle, values: torch.Tensor) -> None:
-        """Contiguous value segments -> owners' landing regions (128-bit peer stores), then the
-        owner side of this rank applies every worker's segment in rank order.  Collective."""
-        self.fence()  # the landing regions of the previous collective call are free again
-        self._bulk_send(h, values)
+        """Receiver-driven: my values stay in my staging buffer; after a rank barrier every owner
+        adds each worker's segment into its shard, reading it over NVLink inside the apply kernel
+        (one cooperative launch, fixed worker order: deterministic).  Collective."""
+        self.fence()  # nobody still reads the staging of the previous collective call
+        self._bulk_stage(h, values)
+        self.fence()  # every rank's staging is complete
         self._push_apply(h)
 
-    def _bulk_send(self, h: KVHandle, values: torch.Tensor) -> None:
-        W, A, r = self.world, self.arena, self.rank
-        self._seq += 1
-        seg = (C.c_int64 * (W + 1))(*h.seg_begin)
-        dst = (C.c_void_p * W)(*[A.peer_ptr(s, self.b_land, r * self.bulk_cap) for s in range(W)])
-        flg = (C.c_void_p * W)(*[A.peer_ptr(s, self.b_pflag, r) for s in range(W)])
-        check(self.lib.psb_kv_bulk_send(ptr(values), seg, dst, flg, W, self._seq, ptr(self.ctr), current_stream()))
+    def _bulk_stage(self, h: KVHandle, values: torch.Tensor) -> None:
+        assert values.dtype == torch.float32 and values.numel() == h.n
+        st = self.push_buffer(h)
+        if values.data_ptr() != st.data_ptr():
+            st.copy_(values)
 
     def _push_apply(self, h: KVHandle) -> None:
-        for w in range(self.world):
-            sl = h.slots_from[w]
-            check(self.lib.psb_kv_bulk_apply_add(self.b_val.ptr, self.b_land.ptr + 4 * w * self.bulk_cap, ptr(sl),
-                                                 sl.numel(), self.b_pflag.ptr + 8 * w, self._seq,
-                                                 current_stream()))
+        W, A = self.world, self.arena
+        src = (C.c_void_p * W)(*[A.peer_ptr(w, self.b_land, h.src_off_from[w]) for w in range(W)])
+        slots = (C.c_void_p * W)(*[ptr(h.slots_from[w]) for w in range(W)])
+        counts = (C.c_int64 * W)(*[h.slots_from[w].numel() for w in range(W)])
+        check(self.lib.psb_kv_bulk_pull_apply(self.b_val.ptr, src, slots, counts, W, self.rank,
+                                              ptr(self.apply_bar), current_stream()))
 
     def pull_bulk(self, h: KVHandle) -> torch.Tensor:
         """Owner side gathers every worker's slots and stores them contiguously into that worker's
@@ -161,8 +173,8 @@ class DeviceKVVector:
         counts = (C.c_int64 * W)(*[h.slots_from[w].numel() for w in range(W)])
         dst = (C.c_void_p * W)(*[A.peer_ptr(w, self.b_pull, r * self.bulk_cap) for w in range(W)])
         flg = (C.c_void_p * W)(*[A.peer_ptr(w, self.b_gflag, r) for w in range(W)])
-        check(self.lib.psb_kv_bulk_gather_send(self.b_val.ptr, slots, counts, dst, flg, W, self._seq,
-                                               ptr(self.ctr), current_stream()))
+        check(self.lib.psb_kv_bulk_gather_send32(self.b_val.ptr, slots, counts, dst, flg, W, self.rank,
+                                                 self._seq, ptr(self.ctr), current_stream()))
 
     def _bulk_pull_result(self, h: KVHandle) -> torch.Tensor:
         W = self.world

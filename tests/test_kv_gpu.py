@@ -47,9 +47,9 @@ def _check(world):
     hs = run_threads(world, reg)
     vs = [torch.randn(h.n, device=dev) for h in hs]
     for kv, h, v in zip(kvs, hs, vs):
-        kv._bulk_send(h, v)
+        kv._bulk_stage(h, v)     # every rank's values in its own staging buffer ...
     for kv, h in zip(kvs, hs):
-        kv._push_apply(h)
+        kv._push_apply(h)        # ... then every owner reads its segments from the "peers"
     for sel, v in zip(sels, vs):
         ref.index_add_(0, sel, v.double())
     torch.cuda.synchronize()
