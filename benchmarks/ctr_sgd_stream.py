@@ -186,6 +186,9 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot)
         dist.all_reduce(load, op=dist.ReduceOp.MAX)
+    if eng._stage_prof is not None:
+        print(f"rank {rank}: prefetch busy {eng.prefetch_busy_s:.2f}s, step loop waited {eng.feed_wait_s:.2f}s, stages "
+              + str({k: round(v, 3) for k, v in eng._stage_prof.items()}), file=sys.stderr, flush=True)
     if rank == 0:
         ms, wall_ms, first_ms, steady_ms = t.tolist()
         ex_pass = tot[0].item() / args.passes

@@ -164,6 +164,8 @@ class AsyncSGDEngine:
         self.feed_wait_s = 0.0       # streaming: wall time the step loop waited for the prefetcher
         self.data = None
         self.n_rows = 0
+        # PSB_SGD_PROFILE=1: wall time per localisation stage (synchronising after each: slower)
+        self._stage_prof = {} if os.environ.get("PSB_SGD_PROFILE") else None
 
     # --------------------------------------------------------------------------------------------
     def load(self, data: SparseCSR, max_unique_per_minibatch: int | None = None) -> None:
@@ -271,14 +273,27 @@ class AsyncSGDEngine:
         """K10 + K13 + K11 + K15 + K8a on the current stream: unique keys and counts, tail filter,
         remap to local columns, owner segments, slots in the owners' tables."""
         cfg, dev = self.cfg, self.device
+        prof = self._stage_prof
+
+        def lap(name, _t=[time.perf_counter()]):
+            if prof is None:
+                return
+            torch.cuda.current_stream(dev).synchronize()
+            now = time.perf_counter()
+            prof[name] = prof.get(name, 0.0) + now - _t[0]
+            _t[0] = now
+        lap("h2d_wait")
         nnz, n_rows = keys_nnz.numel(), row_ptr.numel() - 1
         uniq, cnt = L.unique_count(keys_nnz) if nnz else (keys_nnz, None)
+        lap("sort_unique")
         if self.tail_sketch is not None and nnz:
             self.tail_sketch.insert(uniq, cnt.clamp(max=255))
             uniq = uniq[self.tail_sketch.query_gt(uniq, cfg.tail_feature_freq)].contiguous()
         n_cols = uniq.numel()
+        lap("tail_filter")
         idx1 = L.lookup_sorted(uniq, keys_nnz) if nnz else torch.empty(0, dtype=torch.int32, device=dev)
         rp, col, val = L.compact_csr(row_ptr, idx1, vals)
+        lap("remap")
         # owners: the sorted unique keys split at the shard boundaries
         W = self.world
         if W > 1 and n_cols:
@@ -291,15 +306,18 @@ class AsyncSGDEngine:
                                             owner_begin[1:] - owner_begin[:-1]) if n_cols else \
             torch.zeros(1, dtype=torch.int32, device=dev)
         col_slot = torch.full((max(n_cols, 1),), -1, dtype=torch.int64, device=dev)
+        lap("owners")
         if n_cols:
             assert max(ob[s + 1] - ob[s] for s in range(W)) <= self.land_cap, \
                 "landing region too small: raise max_unique_per_minibatch"
             check(self.lib.psb_kv_lookup_insert(ptr(uniq), n_cols, ptr(col_owner), self.tab_keys_ptrs,
                                                 self.tab_caps, W, ptr(col_slot), ptr(self.overflow),
                                                 current_stream()))
+        lap("table_slots")
         self._new_minibatches = getattr(self, "_new_minibatches", 0) + 1
         if self._new_minibatches % 64 == 0:
             self.check_table_load()
+        lap("load_check")
         return _Minibatch(rp, col, val, y, uniq, col_owner, col_slot, owner_begin, n_rows, n_cols)
 
     def _worker_struct(self, m: _Minibatch):
