@@ -594,6 +594,26 @@ __device__ __forceinline__ void entry_poll(const void* entry, uint32_t tag, doub
   a = __longlong_as_double((long long)((unsigned long long)a0 | ((unsigned long long)a2 << 32)));
   b = __longlong_as_double((long long)((unsigned long long)b0 | ((unsigned long long)b2 << 32)));
 }
+// The lossy form of the push (the FIXING_FLOAT idea, ref src/filter/fixing_float.h:44-95, applied
+// where the bytes are: the gradient push): (g, u) rounded to fp32 travel as ONE 16-byte store
+// {g32, tag, u32, tag}.  Every rank - the sender included - reads the rounded bits back from an
+// entry, so the replicas stay identical.  Inactive columns are simply not pushed, which is
+// what the reference's NaN marks in G / U say with more bytes.
+__device__ __forceinline__ void entry_store_f32(void* entry, float a, float b, uint32_t tag) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %2};" ::"l"(entry), "r"(__float_as_uint(a)),
+               "r"(tag), "r"(__float_as_uint(b)) : "memory");
+}
+__device__ __forceinline__ void entry_poll_f32(const void* entry, uint32_t tag, double& a, double& b) {
+  uint32_t a0, a1, a2, a3, spins = 0;
+  for (;;) {
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3) : "l"(entry) : "memory");
+    if (a1 == tag && a3 == tag) break;
+    if (++spins > kSpinLimit) __trap();
+  }
+  a = (double)__uint_as_float(a0);
+  b = (double)__uint_as_float(a2);
+}
 __device__ __forceinline__ int64_t entry_index(const psb_darlin_worker& W, uint32_t tag, int from,
                                                int64_t j) {
   return (((int64_t)(tag & 1u) * W.n_workers + from) * W.n_cols + j) * 32;
@@ -663,8 +683,11 @@ __device__ __forceinline__ void stage_segment(SegRegs& R, const psb_darlin_worke
 __device__ __forceinline__ void push_entries(const psb_darlin_worker& W, const SegRegs& R, double g,
                                              double u, uint32_t tag, int lane) {
   const uint32_t targets = R.has | (1u << R.owner);
-  if (lane < W.n_workers && (targets >> lane & 1u))
-    entry_store(W.land2[lane] + entry_index(W, tag, W.rank, R.j), g, u, tag);  // peer store
+  if (lane < W.n_workers && (targets >> lane & 1u)) {
+    char* at = W.land2[lane] + entry_index(W, tag, W.rank, R.j);  // peer memory when lane != rank
+    if (W.push_fp32) entry_store_f32(at, (float)g, (float)u, tag);
+    else entry_store(at, g, u, tag);
+  }
 }
 
 // ---- batched fp64 exp / reciprocal ----------------------------------------------------------
@@ -945,8 +968,11 @@ __device__ __forceinline__ double pull_segment_replica(const psb_darlin_worker& 
   const bool mine = R.owner == W.rank;
   if (!C.act || (R.len == 0 && !mine)) return 0;
   double gv = 0, uv = 0;
-  if (lane < W.n_workers && (R.has >> lane & 1u))
-    entry_poll(W.land2[W.rank] + entry_index(W, tag, lane, R.j), tag, gv, uv);
+  if (lane < W.n_workers && (R.has >> lane & 1u)) {
+    const char* at = W.land2[W.rank] + entry_index(W, tag, lane, R.j);
+    if (W.push_fp32) entry_poll_f32(at, tag, gv, uv);
+    else entry_poll(at, tag, gv, uv);
+  }
   double g = 0, u = 0;
   for (int i = 0; i < W.n_workers; ++i) {  // worker order: bit-reproducible, same on every rank
     g += __shfl_sync(FULL, gv, i);

@@ -267,11 +267,23 @@ __global__ void __launch_bounds__(256) k_kv_bulk_pull_apply(const __grid_constan
     if (head > n) head = n;
     for (int64_t i = gt; i < head; i += nt) B.val[sl[i]] += ld_peer_f1(src + i);
     const int64_t n4 = (n - head) / 4;
-    for (int64_t q = gt; q < n4; q += nt) {
+    // two independent 128-bit peer loads per thread and trip: NVLink latency (~2 us) times the
+    // link rate needs a few MB in flight
+    int64_t q = gt;
+    for (; q + nt < n4; q += 2 * nt) {
+      const int64_t i = head + 4 * q, j = head + 4 * (q + nt);
+      const float4 v = ld_peer_f4(src + i);
+      const float4 u = ld_peer_f4(src + j);
+      const int32_t s0 = sl[i], s1 = sl[i + 1], s2 = sl[i + 2], s3 = sl[i + 3];
+      const int32_t t0 = sl[j], t1 = sl[j + 1], t2 = sl[j + 2], t3 = sl[j + 3];
+      B.val[s0] += v.x; B.val[s1] += v.y; B.val[s2] += v.z; B.val[s3] += v.w;  // slots of one worker are distinct
+      B.val[t0] += u.x; B.val[t1] += u.y; B.val[t2] += u.z; B.val[t3] += u.w;
+    }
+    for (; q < n4; q += nt) {
       const int64_t i = head + 4 * q;
       const float4 v = ld_peer_f4(src + i);
       const int32_t s0 = sl[i], s1 = sl[i + 1], s2 = sl[i + 2], s3 = sl[i + 3];
-      B.val[s0] += v.x; B.val[s1] += v.y; B.val[s2] += v.z; B.val[s3] += v.w;  // slots of one worker are distinct
+      B.val[s0] += v.x; B.val[s1] += v.y; B.val[s2] += v.z; B.val[s3] += v.w;
     }
     for (int64_t i = head + 4 * n4 + gt; i < n; i += nt) B.val[sl[i]] += ld_peer_f1(src + i);
     grid_arrive(bar);

@@ -101,6 +101,8 @@ typedef struct psb_darlin_worker {
   double* stash;
   const uint64_t* done_local;
   uint64_t* done_peer[PSB_MAX_PEERS];
+  int32_t push_fp32;   /* 1: (g, u) are pushed rounded to fp32 in one 16-byte store (lossy push filter) */
+  int32_t reserved1;
 } psb_darlin_worker;
 
 /* Server side: one key-range shard of the model. */

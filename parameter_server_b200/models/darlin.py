@@ -62,6 +62,7 @@ class DarlinConfig:
     use_graph: bool = True
     fused: bool = True                # one persistent cooperative kernel per pass
     kernel_flags: int = 0             # psb_darlin_ctrl.flags
+    push_format: str = "fp64"         # multi-rank pass: "fp32" rounds the pushed (g, u) (lossy, half the bytes)
     collectives: str = "peer"         # "peer": kernels store / load peer memory directly;
     #                                   "nccl": the comparison variant (split kernels with
     #                                   all_to_all + all_gather between them, models/darlin_nccl.py)
@@ -420,6 +421,7 @@ class DarlinEngine:
         self.col_has = self._column_holders()
         wk.col_has, wk.stash = self.col_has.data_ptr(), self.stash.data_ptr()
         wk.done_local = self.b_done.ptr
+        wk.push_fp32 = int(cfg.push_format == "fp32")
         for s in range(W):
             wk.land2[s] = A.peer_ptr(s, self.b_land2)
             wk.done_peer[s] = A.peer_ptr(s, self.b_done, self.rank)

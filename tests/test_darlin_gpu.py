@@ -188,3 +188,35 @@ def test_darlin_countmin_tail_filter_is_superset_of_exact():
     extra = len(dicts["countmin"]) - len(dicts["exact"])
     # 2 probes into 2x as many cells as keys: collisions keep roughly a tenth of the rare features
     assert 0 < len(dicts["exact"]) < 4000 and extra <= 0.25 * len(dicts["exact"])
+
+
+def test_darlin_multirank_fp32_push_stays_close_and_consistent():
+    """push_format="fp32": the pushed (g, u) are rounded to fp32 (the lossy push filter); the
+    trajectory stays within fp32 rounding of the exact one and all replicas remain bit-identical."""
+    from parameter_server_b200.models.darlin import DarlinConfig, DarlinEngine, run_pass_emulated
+    from parameter_server_b200.parallel.comm import run_threads
+    from parameter_server_b200.utils.synthetic import make_rcv1_like
+    dev = torch.device("cuda:0")
+    shards = [make_rcv1_like(3000, 700, 24.0, seed=3, shard=r, device=dev) for r in range(2)]
+    objs = {}
+    for fmt in ("fp64", "fp32"):
+        cfg = DarlinConfig(lambda_l1=0.5, feature_block_ratio=0.5, seg_len=64, use_graph=False, seed=3,
+                           push_format=fmt)
+
+        def build(comm):
+            e = DarlinEngine(cfg, comm, dev)
+            e.load(shards[comm.rank])
+            return e
+        engines = run_threads(2, build)
+        thr, out = 1e20, []
+        for it in range(4):
+            p = run_pass_emulated(engines, list(range(len(engines[0].blocks))), thr, False)
+            out.append(p.objective)
+            thr = p.violation / 6000 * 10
+        assert torch.equal(engines[0].w_cache.nan_to_num(nan=-7.0), engines[1].w_cache.nan_to_num(nan=-7.0))
+        objs[fmt] = out
+        for e in engines:
+            e.close()
+    assert objs["fp32"] != objs["fp64"]
+    for a, b in zip(objs["fp32"], objs["fp64"]):
+        assert abs(a - b) <= 1e-5 * abs(b)

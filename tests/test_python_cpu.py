@@ -80,13 +80,13 @@ def test_generators_are_seeded_and_shaped():
 
 
 def test_multi_rank_protocol_model():
-    """tools/protocol_check.py: random interleavings of the landing-slot / mirror protocol of the
-    multi-rank Darlin pass hold its invariants, and the checker notices when the protocol is broken."""
+    """tools/protocol_check.py: random interleavings of the tagged-entry / replicated-update protocol
+    of the multi-rank Darlin pass hold its invariants, and the checker notices when the protocol is broken."""
     import importlib.util
     spec = importlib.util.spec_from_file_location("protocol_check", f"{ROOT}/tools/protocol_check.py")
     pc = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(pc)
     assert pc.check(ranks=3, keys=12, blocks=4, passes=4, schedules=60, verbose=False) == 0
     assert pc.check(ranks=2, keys=9, blocks=3, passes=5, schedules=60, seed=7, verbose=False) == 0
-    assert pc.check(schedules=40, mutate="no_reset", verbose=False) > 0          # consumer forgets to reset a slot
-    assert pc.check(schedules=120, mutate="no_republish", verbose=False) > 0     # owner forgets to re-send the mark
+    assert pc.check(schedules=60, mutate="no_flow", verbose=False) > 0      # writers ignore the done flags
+    assert pc.check(schedules=60, mutate="no_parity", verbose=False) > 0    # one buffer instead of two per step parity

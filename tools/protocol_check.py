@@ -1,15 +1,19 @@
-"""Randomised interleaving check of the multi-rank Darlin protocol (csrc/cuda/darlin.cu,
-`server_phase_direct` / `mirror_store` / `mirror_poll`): landing slots that are their own arrival
-flags, consumer reset, tagged mirror entries, active bits kept in step on both sides.
+"""Randomised interleaving check of the multi-rank Darlin protocol (csrc/cuda/darlin.cu:
+`push_entries` / `pull_segment_replica` / `grid_wait_flow`): tagged (g, u) entries stored into the
+landing table of every rank that holds or owns a column, double-buffered by step parity; every
+rank sums the holders' entries itself and applies the same update to its replica; a writer starts
+step s only after every peer finished step s-2 (the `done` flags).
 
 It is a model of the protocol, not of the CUDA code: every rank is a little state machine whose
-atomic actions (one push, one slot poll+reset, one publish, one mirror poll) are interleaved by a
-seeded random scheduler.  Checked on every schedule:
+atomic actions (the pushes of a step, one entry poll, the end-of-step flag) are interleaved by a
+seeded random scheduler; block orders deliberately repeat blocks in consecutive steps and two
+steps apart, and ranks may hold no column of a block at all (so nothing but the flow control
+keeps them from running ahead).  Checked on every schedule:
   * no deadlock: while some rank has work, some action is enabled;
-  * a push never lands on a slot that still holds an unconsumed value;
-  * the owner sums exactly the contributions of the current visit of the key;
-  * a worker never accepts a mirror entry of another step;
-  * worker and owner copies of the active bit agree whenever a step starts.
+  * an entry is never overwritten before every rank that needs it has read it;
+  * a reader only ever accepts the entry of the step it is in, and sums exactly the holders'
+    contributions of that step;
+  * all replicas (and the owner's shard) of a coordinate hold the same value after every step.
 
     python tools/protocol_check.py [--ranks 3] [--keys 12] [--passes 4] [--schedules 300]
 """
@@ -18,147 +22,119 @@ from __future__ import annotations
 import argparse
 import random
 
-EMPTY = None
-
 
 class Model:
-    def __init__(self, ranks: int, keys: int, blocks: int, passes: int, revive: bool, rng: random.Random,
-                 mutate: str = ""):
+    def __init__(self, ranks: int, keys: int, blocks: int, passes: int, rng: random.Random, mutate: str = ""):
         self.R, self.K, self.rng, self.mutate = ranks, keys, rng, mutate
         self.owner = [k % ranks for k in range(keys)]
-        # which workers hold nonzeros of a key (at least one)
-        self.has = [set(r for r in range(ranks) if rng.random() < 0.7) or {rng.randrange(ranks)} for _ in range(keys)]
+        # which workers hold nonzeros of a key (at least one); some ranks hold nothing of a block
+        self.has = [set(r for r in range(ranks) if rng.random() < 0.6) or {rng.randrange(ranks)} for _ in range(keys)]
         self.block_of = [k % blocks for k in range(keys)]
         order = []
         for p in range(passes):
             b = list(range(blocks))
             rng.shuffle(b)
-            order += [(p, x) for x in b]
-        self.steps = order                      # global step s -> (pass, block)
-        self.reset_pass = {p for p in range(1, passes) if rng.random() < 0.5}   # KKT filter resets
-        self.revive = revive
-        self.land = {(self.owner[k], r, k): EMPTY for k in range(keys) for r in self.has[k]}
-        self.mirror = {(r, k): (0, None) for k in range(keys) for r in self.has[k]}   # (tag, value)
-        self.w_active = [[True] * keys for _ in range(ranks)]      # worker copies
-        self.s_active = [True] * keys                              # owner copy
-        self.s_marked = [False] * keys                             # weight is the NaN mark
-        self.filter_at = {k: rng.randrange(len(order)) for k in range(keys) if rng.random() < 0.4}
+            if p == 0 and blocks >= 2:  # prior-group style repeats: a, a, b, a
+                b = [b[0], b[0], b[1], b[0]] + b
+            order.append(b)
+        self.passes = order
+        # landing[q][parity][r][k] = (tag, value) as rank q sees it; readers[...] = ranks that still
+        # have to read the current content
+        self.land = [[[{} for _ in range(ranks)] for _ in range(2)] for _ in range(ranks)]
+        self.unread = [[[{} for _ in range(ranks)] for _ in range(2)] for _ in range(ranks)]
+        self.done = [[0] * ranks for _ in range(ranks)]      # done[q][r]: rank q's view of rank r
+        self.replica = [[0] * keys for _ in range(ranks)]    # every rank's copy of the coordinate
+        self.shard = [0] * keys                               # the owner's authoritative copy
+        self.contrib = {}                                     # (step, r, k) -> value pushed
         self.pc = [self._program(r) for r in range(ranks)]
         self.pos = [0] * ranks
         self.errors = []
 
-    # ---- per-rank programs: lists of (kind, step, key, extra) ------------------------------------
+    def needers(self, k):
+        return self.has[k] | {self.owner[k]}
+
+    # ---- per-rank programs: (kind, seq, key) with seq = 1, 2, ... over all passes ----------------
     def _program(self, r: int):
-        prog = []
-        for s, (p, b) in enumerate(self.steps):
-            first_of_pass = s == 0 or self.steps[s - 1][0] != p
-            if first_of_pass and p in self.reset_pass:
-                prog.append(("reset", s, None, None))
-            keys = [k for k in range(self.K) if self.block_of[k] == b]
-            prog.append(("begin", s, None, None))
-            for k in keys:
-                if r in self.has[k]:
-                    prog.append(("push", s, k, None))
-            for k in keys:
-                if self.owner[k] == r:
-                    for w in sorted(self.has[k]):
-                        prog.append(("poll", s, k, w))
-                    prog.append(("publish", s, k, None))
-            for k in keys:
-                if r in self.has[k]:
-                    prog.append(("pull", s, k, None))
-            prog.append(("barrier", s, None, None))
+        prog, seq = [], 0
+        for p, blocks in enumerate(self.passes):
+            for b in blocks:
+                seq += 1
+                keys = [k for k in range(self.K) if self.block_of[k] == b]
+                prog.append(("flow", seq, None))            # wait: every peer finished seq - 2
+                prog.append(("push", seq, [k for k in keys if r in self.has[k]]))
+                for k in keys:
+                    if r in self.needers(k):
+                        prog.append(("pull", seq, k))
+                prog.append(("done", seq, None))
+            prog.append(("barrier", seq, p))                # rank barrier at the end of a pass
         return prog
 
-    # ---- one atomic action; returns False when it is not enabled yet ------------------------------
-    def try_step(self, r: int) -> bool:
-        kind, s, k, x = self.pc[r][self.pos[r]]
-        tag = s + 1
-        if kind == "reset":                      # pass begin: refill the active sets (both copies live on r)
-            for kk in range(self.K):
-                self.w_active[r][kk] = True
-                if self.owner[kk] == r:
-                    self.s_active[kk] = True
-                    if self.revive:
-                        self.s_marked[kk] = False
-        elif kind == "begin":
-            for kk in range(self.K):
-                if self.owner[kk] == r and self.block_of[kk] == self.steps[s][1]:
-                    self._acc = getattr(self, "_acc", {})
-                    self._acc[(kk, s)] = []
-        elif kind == "push":
-            if not self.w_active[r][k]:
-                pass                              # nothing is sent for an inactive column
-            else:
-                slot = (self.owner[k], r, k)
-                if self.land[slot] is not EMPTY:
-                    self.errors.append(f"step {s}: push of rank {r} key {k} lands on an unconsumed value")
-                self.land[slot] = (s, r)
-        elif kind == "poll":
-            if not self.s_active[k]:
-                pass                              # owner's bit clear: nobody pushes, nothing to poll
-            else:
-                slot = (r, x, k)
-                if self.land[slot] is EMPTY:
-                    return False                  # spin
-                if self.land[slot] != (s, x):
-                    self.errors.append(f"step {s}: owner {r} reads {self.land[slot]} for key {k} worker {x}")
-                self._acc[(k, s)].append(x)
-                if self.mutate != "no_reset":
-                    self.land[slot] = EMPTY       # consumer reset
-        elif kind == "publish":
-            if self.s_active[k]:
-                if sorted(self._acc[(k, s)]) != sorted(self.has[k]):
-                    self.errors.append(f"step {s}: key {k} summed {self._acc[(k, s)]}, holders {self.has[k]}")
-                republish = self.s_marked[k] and self.mutate != "no_republish"
-                if self.s_marked[k] and not republish:
-                    self.s_active[k] = False      # the bug the kernel comment warns about: workers that
-                    self.pos[r] += 1              # pushed after a reset would wait for ever
-                    return True
-                if self.s_marked[k] or self.filter_at.get(k) == s:
-                    self.s_active[k] = False      # (still) filtered: mark goes out again
-                    self.s_marked[k] = True
-                    val = "mark"
-                else:
-                    val = ("w", s)
-                for w in self.has[k]:
-                    self.mirror[(w, k)] = (tag, val)
-        elif kind == "pull":
-            if self.w_active[r][k]:
-                t, val = self.mirror[(r, k)]
-                if t != tag:
-                    if t > tag:
-                        self.errors.append(f"step {s}: rank {r} sees a future entry for key {k}")
-                    return False                  # spin on the tag
-                if val == "mark":
-                    self.w_active[r][k] = False
-                elif val != ("w", s):
-                    self.errors.append(f"step {s}: rank {r} accepted {val} for key {k}")
-        elif kind == "barrier":
-            pass                                  # local barrier C: nothing to model across ranks
-        self.pos[r] += 1
+    def enabled(self, r: int) -> bool:
+        kind, seq, arg = self.pc[r][self.pos[r]]
+        if kind == "flow":
+            if self.mutate == "no_flow":
+                return True
+            return all(self.done[r][q] + 2 >= seq for q in range(self.R))
+        if kind == "pull":
+            par = seq & 1 if self.mutate != "no_parity" else 0
+            return all(self.land[r][par][h].get(arg, (0, None))[0] >= seq for h in self.has[arg])
+        if kind == "barrier":
+            return all(self.pos[q] >= len(self.pc[q]) or self.pc[q][self.pos[q]][1] >= seq for q in range(self.R))
         return True
 
-    def run(self) -> list:
+    def step(self, r: int) -> None:
+        kind, seq, arg = self.pc[r][self.pos[r]]
+        if kind == "push":
+            par = seq & 1 if self.mutate != "no_parity" else 0
+            for k in arg:
+                v = self.rng.randrange(1, 1000)
+                self.contrib[(seq, r, k)] = v
+                for q in self.needers(k):
+                    if self.unread[q][par][r].get(k):
+                        self.errors.append(f"seq {seq}: rank {r} overwrites key {k} on rank {q} before it was read "
+                                           f"(tag {self.land[q][par][r][k][0]})")
+                    self.land[q][par][r][k] = (seq, v)
+                    self.unread[q][par][r][k] = True
+        elif kind == "pull":
+            par = seq & 1 if self.mutate != "no_parity" else 0
+            total = 0
+            for h in sorted(self.has[arg]):
+                tag, v = self.land[r][par][h][arg]
+                if tag != seq:
+                    self.errors.append(f"seq {seq}: rank {r} reads key {arg} of worker {h} with tag {tag}")
+                total += v
+                self.unread[r][par][h][arg] = False
+            want = sum(self.contrib[(seq, h, arg)] for h in self.has[arg])
+            if total != want:
+                self.errors.append(f"seq {seq}: rank {r} summed {total} for key {arg}, the step pushed {want}")
+            self.replica[r][arg] += total                     # the deterministic update
+            if self.owner[arg] == r:
+                self.shard[arg] += total
+        elif kind == "done":
+            for q in range(self.R):
+                self.done[q][r] = seq
+        elif kind == "barrier":
+            pass
+        self.pos[r] += 1
+
+    def run(self):
         while True:
             live = [r for r in range(self.R) if self.pos[r] < len(self.pc[r])]
             if not live:
                 break
-            self.rng.shuffle(live)
-            for r in live:
-                if self.try_step(r):
-                    break
-            else:
-                where = {r: self.pc[r][self.pos[r]] for r in live}
-                self.errors.append(f"deadlock: {where}")
+            ready = [r for r in live if self.enabled(r)]
+            if not ready:
+                self.errors.append("deadlock: " + str({r: self.pc[r][self.pos[r]][:2] for r in live}))
                 break
+            # rank 0 is a straggler: picked ten times less often, so that the others run ahead of it
+            self.step(self.rng.choices(ready, weights=[0.1 if r == 0 else 1.0 for r in ready])[0])
             if self.errors:
                 break
-        # agreement of the two copies of every active bit at the end
-        for k in range(self.K):
-            for r in self.has[k]:
-                if self.w_active[r][k] != self.s_active[k]:
-                    self.errors.append(f"end: active bit of key {k} differs (worker {r})")
+        if not self.errors:
+            for k in range(self.K):
+                vals = {self.replica[r][k] for r in self.needers(k)} | {self.shard[k]}
+                if len(vals) != 1:
+                    self.errors.append(f"end: copies of key {k} differ: {sorted(vals)}")
         return self.errors
 
 
@@ -166,8 +142,7 @@ def check(ranks=3, keys=12, blocks=4, passes=4, schedules=300, seed=0, mutate=""
     bad = 0
     for i in range(schedules):
         rng = random.Random(seed * 100003 + i)
-        m = Model(ranks, keys, blocks, passes, revive=bool(i & 1), rng=rng, mutate=mutate)
-        errs = m.run()
+        errs = Model(ranks, keys, blocks, passes, rng=rng, mutate=mutate).run()
         if errs:
             bad += 1
             if verbose:
@@ -182,7 +157,7 @@ if __name__ == "__main__":
     ap.add_argument("--blocks", type=int, default=4)
     ap.add_argument("--passes", type=int, default=4)
     ap.add_argument("--schedules", type=int, default=300)
-    ap.add_argument("--mutate", default="", choices=["", "no_reset", "no_republish"],
+    ap.add_argument("--mutate", default="", choices=["", "no_flow", "no_parity"],
                     help="break the protocol on purpose: the checker must notice")
     a = ap.parse_args()
     n = check(a.ranks, a.keys, a.blocks, a.passes, a.schedules, mutate=a.mutate)
