@@ -67,3 +67,38 @@ def test_async_sgd_config_and_model_evaluation(dataset):
     log = _run(d / "eval.conf")
     auc = float([l for l in log.splitlines() if l.startswith("auc:")][0].split()[1])
     assert auc > 0.85
+
+
+def test_shipped_ctr_batch_config_on_gpu(tmp_path):
+    """example/linear/ctr/batch_l1lr.conf UNCHANGED through the GPU front end: multi-group SPARSE_BINARY
+    text, prior feature groups 127 / 120 swept first without delay, tail_feature_freq 4,
+    max_block_delay 8 (9 blocks per device step).  Block orders are random and drawn from different
+    generators on the two sides, so the trajectories differ; both must reach the same optimum."""
+    from parameter_server_b200.runtime import host
+    from parameter_server_b200.utils.synthetic import make_ctr_like, write_ps_sparse_binary
+    relabel = {1: 120, 2: 127, 3: 3, 4: 5}
+    os.makedirs(tmp_path / "data" / "ctr" / "train")
+    for p in range(4):
+        groups = make_ctr_like(1500, n_groups=4, keys_per_group=1 << 12, seed=2, shard=p, nnz_per_group=4.0)
+        out = {}
+        for g, d in groups.items():
+            d.keys = (d.keys & ((1 << 54) - 1)) | (relabel[g] << 54)   # the group id rides in the top 10 bits
+            out[relabel[g]] = d
+        write_ps_sparse_binary(out, str(tmp_path / "data" / "ctr" / "train" / f"part-{p:03d}"))
+    conf = open(f"{ROOT}/example/linear/ctr/batch_l1lr.conf").read()
+    r = subprocess.run([sys.executable, "-m", "parameter_server_b200.apps.ps", "--app_file",
+                        f"{ROOT}/example/linear/ctr/batch_l1lr.conf"], cwd=tmp_path, capture_output=True, text=True,
+                       timeout=170, env=dict(os.environ, PYTHONPATH=ROOT))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    rows = [l.split("|") for l in r.stderr.splitlines() if l[:5].strip().isdigit()]
+    gpu_obj = [float(x[1].split()[0]) for x in rows]
+    assert "tau=8" in r.stderr and len(gpu_obj) >= 5 and gpu_obj[-1] < gpu_obj[0]
+    cwd = os.getcwd()
+    os.chdir(tmp_path)
+    try:
+        cpu = host.run_cluster(conf.replace("model/ctr_batch", "model/cpu").replace("cache/ctr_train", "cache/cpu"), 1, 2)
+    finally:
+        os.chdir(cwd)
+    cpu_obj = [float(l.split()[1]) for l in cpu.strip().splitlines()]
+    assert gpu_obj[-1] == pytest.approx(cpu_obj[-1], rel=2e-2), (gpu_obj, cpu_obj)
+    assert os.path.exists(tmp_path / "model" / "ctr_batch_S0")
