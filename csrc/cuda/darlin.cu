@@ -495,8 +495,7 @@ struct SegMeta {
   int len;
   bool first, single;
 };
-__device__ __forceinline__ SegMeta load_meta(const void* seg_meta, int64_t s) {
-  const int4 m = __ldg(reinterpret_cast<const int4*>(seg_meta) + s);
+__device__ __forceinline__ SegMeta decode_meta(const int4 m) {
   SegMeta r;
   r.j = m.x;
   r.len = m.y & 0xffff;
@@ -504,6 +503,9 @@ __device__ __forceinline__ SegMeta load_meta(const void* seg_meta, int64_t s) {
   r.single = (m.y >> 17) & 1;
   r.beg = (int64_t)(uint32_t)m.z | ((int64_t)m.w << 32);
   return r;
+}
+__device__ __forceinline__ SegMeta load_meta(const void* seg_meta, int64_t s) {
+  return decode_meta(__ldg(reinterpret_cast<const int4*>(seg_meta) + s));
 }
 
 __device__ __forceinline__ uint32_t atom_add_acqrel_gpu(uint32_t* p, uint32_t v) {
@@ -516,41 +518,6 @@ __device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
 }
 
 constexpr int kUnroll = 4;  // 4 x 32 lanes = one 128-entry segment per batch
-
-// One coordinate of the server update with its state already in registers (ref
-// darlin.h:216-245).  Used by the single-rank persistent kernel, where the warp that finishes
-// a column's gradient applies the update at once: no landing slot, no second synchronisation.
-__device__ __forceinline__ double update_coord(const psb_darlin_server& S, const ServerHyper& h,
-                                               int64_t k, double g, double u, double w, double dl,
-                                               bool active) {
-  if (!active || is_marked(w)) return 0;
-  u = u / h.eta + 1e-10;
-  const double g_pos = g + h.lambda, g_neg = g - h.lambda;
-  double d = -w, vio = 0;
-  if (w == 0) {
-    if (g_pos < 0) {
-      vio = -g_pos;
-    } else if (g_neg > 0) {
-      vio = g_neg;
-    } else if (g_pos > h.thr && g_neg < -h.thr) {
-      bit_clear_atomic(S.active, k);
-      S.w[k] = nan_mark();
-      S.dw[k] = 0;
-      return 0;
-    }
-  }
-  if (g_pos <= u * w) {
-    d = -g_pos / u;
-  } else if (g_neg >= u * w) {
-    d = -g_neg / u;
-  }
-  d = fmin(dl, fmax(-dl, d));
-  S.delta[k] = fmin(h.delta_max, 2 * fabs(d) + .1);
-  const double w_new = w + d;
-  S.w[k] = w_new;
-  S.dw[k] = w_new - w;
-  return vio;
-}
 
 // ---- fused multi-rank pass: one NVLink flight per step, replicated coordinate update ----------
 // Every rank keeps a replica of (w, delta, active bit) of every column of the global dictionary.
@@ -650,11 +617,13 @@ struct Carry {
 
 template <bool BINARY, bool SINGLE>
 __device__ __forceinline__ void stage_segment(SegRegs& R, const psb_darlin_worker& W,
-                                              const StepPlan& plan, int bps, int64_t v, int lane) {
+                                              const StepPlan& plan, int bps, int64_t v, int lane,
+                                              const int4 fetched = make_int4(0, -1, 0, 0)) {
   R.v = v;
   const int q = locate(plan, bps, v);
   const int64_t s = plan.first[q] + (v - plan.pref[q]);
-  const SegMeta m = load_meta(W.seg_meta, s);
+  // the descriptor may have been fetched one barrier earlier (prefetch_step): one round trip less
+  const SegMeta m = fetched.y >= 0 ? decode_meta(fetched) : load_meta(W.seg_meta, s);
   R.j = m.j; R.beg = m.beg; R.len = m.len; R.first = m.first; R.single = m.single;
 #pragma unroll
   for (int k = 0; k < kUnroll; ++k) {
@@ -665,7 +634,7 @@ __device__ __forceinline__ void stage_segment(SegRegs& R, const psb_darlin_worke
   R.off = __ldg(W.col_off + m.j);
   R.has = SINGLE ? 1u : __ldg(W.col_has + m.j);
   R.nseg = 1; R.sc = 0;
-  if (!m.single) {
+  if (!SINGLE && !m.single) {  // only the multi-rank reduction needs the position among the column's segments
     const int64_t cs = __ldg(W.col_seg + m.j);
     R.nseg = (int)(__ldg(W.col_seg + m.j + 1) - cs);
     R.sc = (int)(s - cs);
@@ -751,34 +720,32 @@ __device__ __forceinline__ void rcp_batch(double (&a)[N]) {  // a >= 1
   for (int i = 0; i < N; ++i) a[i] = r[i];
 }
 
-// Phase 1 of one segment.  SINGLE: the warp that completes a column applies the shard update at
-// once and returns its KKT violation.  Otherwise the completed (g, u) is pushed to the ranks that
-// need it and the coordinate's state is returned in `C` for phase 3.
+// Phase 1 of one segment: partial (g, u) of the column over this segment's rows.  The
+// coordinate's state as it is now is returned in `C` for phase 3, where the update happens.
+//   one rank      the partials are accumulated with fp64 reductions into W.acc (two fire-and-forget
+//                 REDs per segment); phase 3 reads the totals after the grid barrier.  No dependent
+//                 chain at all behind the arithmetic.
+//   several ranks the column total has to leave for the peers BEFORE the barrier, so the segments
+//                 of a column are reduced in fixed order by the last one to arrive (L2 partials +
+//                 acq_rel counter) and that warp pushes the entries.
 template <bool BINARY, bool SINGLE>
 __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const psb_darlin_server& S,
                                                const ServerHyper& h, const SegRegs& R, int lane,
                                                const double* __restrict__ exp_tab, uint32_t tag,
                                                Carry& C) {
-  // one latency level: active word, trust region, the margins and the coordinate
+  // ONE latency level: active word, trust region, replica weight and the margins of the first
+  // batch are all requested before anything is known about the column
   const uint32_t aw = __ldcg(W.active + (R.j >> 5));
   double d = __ldcg(W.delta + R.j);
-  double sw = 0, sdl = 0;
-  uint32_t saw = 0;
-  if (SINGLE) {
-    if (lane == 0) {  // any segment may turn out to be the one that reduces the column
-      sw = __ldcg(S.w + R.off);
-      sdl = __ldcg(S.delta + R.off);
-      saw = __ldcg(S.active + (R.off >> 5));
-    }
-  } else {
-    C.w = __ldcg(W.w + R.j);
-    C.dl = d;
-    // a weight that was KKT-filtered stays marked after a filter reset:
-    // nothing is pushed or pulled for it, its bits stay as they are
-    C.act = (aw >> (R.j & 31) & 1u) && !is_marked(C.w);
-    if (!C.act || R.len == 0) return 0;  // a rank without nonzeros in the column pushes nothing
-  }
-  if (SINGLE && !(aw >> (R.j & 31) & 1u)) return 0;  // inactive column: nothing is pushed
+  C.w = __ldcg(W.w + R.j);
+  double zz0[kUnroll];
+#pragma unroll
+  for (int k = 0; k < kUnroll; ++k) zz0[k] = R.idx[k] != 0xffffffffu ? __ldcg(W.z + R.idx[k]) : 0.0;
+  C.dl = d;
+  // a weight that was KKT-filtered stays marked after a filter reset: nothing
+  // is pushed or pulled for it, its bits stay as they are
+  C.act = (aw >> (R.j & 31) & 1u) && !is_marked(C.w);
+  if (!C.act || R.len == 0) return 0;  // a rank without nonzeros in the column pushes nothing
   if (BINARY) d = exp(d);
   double g = 0, u = 0;
   uint32_t idx[kUnroll];
@@ -801,7 +768,8 @@ __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const
     }
     double zz[kUnroll];
 #pragma unroll
-    for (int k = 0; k < kUnroll; ++k) zz[k] = idx[k] != 0xffffffffu ? __ldcg(W.z + idx[k]) : 0.0;
+    for (int k = 0; k < kUnroll; ++k)
+      zz[k] = base == 0 ? zz0[k] : (idx[k] != 0xffffffffu ? __ldcg(W.z + idx[k]) : 0.0);
     // branch-free over the batch so the four exp/divide chains interleave (fp64 latency bound);
     // a padding entry has x == 0 and contributes exactly nothing
     double tau[kUnroll], x[kUnroll], cv[kUnroll];
@@ -822,14 +790,17 @@ __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const
   }
   g = warp_sum(g);
   u = warp_sum(u);
-  double vio = 0;
-  if (R.single) {
-    if (SINGLE) {
-      if (lane == 0) vio = update_coord(S, h, R.off, g, u, sw, sdl, saw >> (R.off & 31) & 1u);
-    } else {
-      push_entries(W, R, g, u, tag, lane);
+  if (SINGLE) {
+    if (lane == 0) {
+      double* acc = W.acc + 2 * ((int64_t)(tag & 1u) * W.n_cols + R.j);
+      atomicAdd(acc, g);      // compiled to RED: nobody waits for the result
+      atomicAdd(acc + 1, u);
     }
-    return vio;
+    return 0;
+  }
+  if (R.single) {
+    push_entries(W, R, g, u, tag, lane);
+    return 0;
   }
   int old = 0;
   if (lane == 0) {
@@ -848,14 +819,10 @@ __device__ __forceinline__ double grad_segment(const psb_darlin_worker& W, const
     }
     sg = warp_sum(sg);
     su = warp_sum(su);
-    if (SINGLE) {
-      if (lane == 0) vio = update_coord(S, h, R.off, sg, su, sw, sdl, saw >> (R.off & 31) & 1u);
-    } else {
-      push_entries(W, R, sg, su, tag, lane);
-    }
+    push_entries(W, R, sg, su, tag, lane);
     if (lane == 0) W.col_cnt[R.j] = 0;
   }
-  return vio;
+  return 0;
 }
 
 // Segments beyond a warp's first one of a step (steps with more segments than resident warps)
@@ -895,7 +862,7 @@ __device__ __forceinline__ double grad_phase_packed(const psb_darlin_worker& W, 
     Carry C;
     stage_segment<BINARY, SINGLE>(R, W, plan, bps, v, lane);
     vio_max = fmax(vio_max, grad_segment<BINARY, SINGLE>(W, S, h, R, lane, exp_tab, tag, C));
-    if (!SINGLE) stash_put(W, v, C, lane);
+    stash_put(W, v, C, lane);
   }
   return vio_max;
 }
@@ -929,54 +896,37 @@ __device__ __forceinline__ void scatter_margins(const psb_darlin_worker& W, cons
   }
 }
 
-// Phase 3 of one segment, single rank: the shard was updated in phase 1, read (w, dw) from it.
-template <bool BINARY>
-__device__ __forceinline__ void pull_segment_local(const psb_darlin_worker& W, const SegRegs& R,
-                                                   double delta_max, int lane) {
-  const uint32_t aw = __ldcg(W.active + (R.j >> 5));
-  double w_new = 0, d = 0;
-  if (lane == 0) {
-    w_new = ld_volatile_f64(W.srv_w[R.owner] + R.off);
-    d = ld_volatile_f64(W.srv_dw[R.owner] + R.off);
-  }
-  w_new = __shfl_sync(FULL, w_new, 0);
-  d = __shfl_sync(FULL, d, 0);
-  if (is_marked(w_new)) {  // the server filtered this coordinate (ref darlin.h:439-444)
-    if (R.first && lane == 0) {
-      bit_clear_atomic(W.active, R.j);
-      W.w[R.j] = 0;
-    }
-    return;
-  }
-  if (!(aw >> (R.j & 31) & 1u)) return;
-  if (R.first && lane == 0) {
-    W.w[R.j] = w_new;
-    W.delta[R.j] = fmin(delta_max, 2 * fabs(d) + .1);
-  }
-  if (d == 0) return;
-  scatter_margins<BINARY>(W, R, d, lane);
-}
-
-// Phase 3 of one segment, several ranks: collect the column's (g, u) from the holders' entries in
-// this rank's landing table, apply the update (ref darlin.h:216-245 on the replica, 436-449), and
-// scatter dw into the margins.  The column's first segment writes the replica and, on the owner,
-// the shard.
-template <bool BINARY>
+// Phase 3 of one segment: get the column's total (g, u) - one rank: from the accumulator; several
+// ranks: the holders' entries in this rank's landing table, summed in worker order - apply the
+// update (ref darlin.h:216-245 on the replica, 436-449), and scatter dw into the margins.  Every
+// segment of a column computes the same update; the first one writes the replica and, on the
+// owner, the shard.
+template <bool BINARY, bool SINGLE>
 __device__ __forceinline__ double pull_segment_replica(const psb_darlin_worker& W, const psb_darlin_server& S,
                                                        const ServerHyper& h, const SegRegs& R,
                                                        const Carry& C, int lane, uint32_t tag) {
-  const bool mine = R.owner == W.rank;
+  const bool mine = SINGLE || R.owner == W.rank;
   if (!C.act || (R.len == 0 && !mine)) return 0;
-  double gv = 0, uv = 0;
-  if (lane < W.n_workers && (R.has >> lane & 1u)) {
-    const char* at = W.land2[W.rank] + entry_index(W, tag, lane, R.j);
-    if (W.push_fp32) entry_poll_f32(at, tag, gv, uv);
-    else entry_poll(at, tag, gv, uv);
-  }
   double g = 0, u = 0;
-  for (int i = 0; i < W.n_workers; ++i) {  // worker order: bit-reproducible, same on every rank
-    g += __shfl_sync(FULL, gv, i);
-    u += __shfl_sync(FULL, uv, i);
+  if (SINGLE) {
+    if (lane == 0) {
+      const double* acc = W.acc + 2 * ((int64_t)(tag & 1u) * W.n_cols + R.j);
+      g = __ldcg(acc);
+      u = __ldcg(acc + 1);
+    }
+    g = __shfl_sync(FULL, g, 0);
+    u = __shfl_sync(FULL, u, 0);
+  } else {
+    double gv = 0, uv = 0;
+    if (lane < W.n_workers && (R.has >> lane & 1u)) {
+      const char* at = W.land2[W.rank] + entry_index(W, tag, lane, R.j);
+      if (W.push_fp32) entry_poll_f32(at, tag, gv, uv);
+      else entry_poll(at, tag, gv, uv);
+    }
+    for (int i = 0; i < W.n_workers; ++i) {  // worker order: bit-reproducible, same on every rank
+      g += __shfl_sync(FULL, gv, i);
+      u += __shfl_sync(FULL, uv, i);
+    }
   }
   const double w = C.w, dl = C.dl;
   u = u / h.eta + 1e-10;
@@ -1031,27 +981,44 @@ __device__ __forceinline__ double pull_phase_packed(const psb_darlin_worker& W, 
   double vio = 0;
   if (gw < total) {
     if (pre.v == gw) {
-      if (SINGLE) pull_segment_local<BINARY>(W, pre, h.delta_max, lane);
-      else vio = pull_segment_replica<BINARY>(W, S, h, pre, C0, lane, tag);
+      vio = pull_segment_replica<BINARY, SINGLE>(W, S, h, pre, C0, lane, tag);
     } else {
       SegRegs R;
       stage_segment<BINARY, SINGLE>(R, W, plan, bps, gw, lane);
-      if (SINGLE) pull_segment_local<BINARY>(W, R, h.delta_max, lane);
-      else vio = pull_segment_replica<BINARY>(W, S, h, R, C0, lane, tag);
+      vio = pull_segment_replica<BINARY, SINGLE>(W, S, h, R, C0, lane, tag);
     }
   }
   for (int64_t v = gw + nw; v < total; v += nw) {
     SegRegs R;
+    Carry C;
     stage_segment<BINARY, SINGLE>(R, W, plan, bps, v, lane);
-    if (SINGLE) {
-      pull_segment_local<BINARY>(W, R, h.delta_max, lane);
-    } else {
-      Carry C;
-      stash_get(W, v, C);
-      vio = fmax(vio, pull_segment_replica<BINARY>(W, S, h, R, C, lane, tag));
-    }
+    stash_get(W, v, C);
+    vio = fmax(vio, pull_segment_replica<BINARY, SINGLE>(W, S, h, R, C, lane, tag));
   }
   return vio;
+}
+
+// One rank: the accumulators of the step's columns go back to zero once every reader is through
+// (after the step's last barrier) - the other parity is in use by then, so nothing races.
+__device__ __forceinline__ void clear_accumulators(const psb_darlin_worker& W, const StepPlan& plan, int bps,
+                                                   int64_t gw, int64_t nw, int lane, int64_t first_j,
+                                                   bool first_known, uint32_t tag) {
+  const int64_t total = plan.pref[bps];
+  double* acc = W.acc + 2 * (int64_t)(tag & 1u) * W.n_cols;
+  for (int64_t v = gw; v < total; v += nw) {
+    int64_t j = -1;
+    if (v == gw && first_known) {
+      j = first_j;
+    } else {
+      const int q = locate(plan, bps, v);
+      const SegMeta m = load_meta(W.seg_meta, plan.first[q] + (v - plan.pref[q]));
+      if (m.first) j = m.j;
+    }
+    if (j >= 0 && lane == 0) {
+      __stcg(acc + 2 * j, 0.0);
+      __stcg(acc + 2 * j + 1, 0.0);
+    }
+  }
 }
 
 __device__ __forceinline__ void prefetch_l2(const void* p) {
@@ -1059,18 +1026,22 @@ __device__ __forceinline__ void prefetch_l2(const void* p) {
 }
 // warm L2 with the CSC ranges this CTA's warps will read in the next step
 template <bool BINARY>
-__device__ __forceinline__ void prefetch_step(const psb_darlin_worker& W, const StepPlan& plan, int bps,
+__device__ __forceinline__ int4 prefetch_step(const psb_darlin_worker& W, const StepPlan& plan, int bps,
                                               int64_t gw, int64_t nw, int lane) {
   const int64_t total = plan.pref[bps];
+  int4 first_meta = make_int4(0, -1, 0, 0);  // y < 0: nothing fetched
   for (int64_t v = gw; v < total; v += nw) {
     const int q = locate(plan, bps, v);
     const int64_t s = plan.first[q] + (v - plan.pref[q]);
-    const SegMeta m = load_meta(W.seg_meta, s);
+    const int4 raw = __ldg(reinterpret_cast<const int4*>(W.seg_meta) + s);
+    if (v == gw) first_meta = raw;  // kept for the staging that follows one barrier later
+    const SegMeta m = decode_meta(raw);
     const int lines = (m.len * 4 + 127) / 128 + 1;
     if (lane < lines) prefetch_l2(reinterpret_cast<const char*>(W.row_idx + m.beg) + lane * 128);
     if (!BINARY && lane >= 16 && lane - 16 < lines)
       prefetch_l2(reinterpret_cast<const char*>(W.sval + m.beg) + (lane - 16) * 128);
   }
+  return first_meta;
 }
 
 
@@ -1156,9 +1127,8 @@ __device__ __forceinline__ void darlin_pass_body(
     if (ctrl->revive_on_reset) {
       for (int64_t i = gt; i < S.n_keys; i += nt)
         if (is_marked(__ldcg(S.w + i))) S.w[i] = 0;
-      if (!SINGLE)
-        for (int64_t i = gt; i < W.n_cols; i += nt)
-          if (is_marked(__ldcg(W.w + i))) W.w[i] = 0;
+      for (int64_t i = gt; i < W.n_cols; i += nt)
+        if (is_marked(__ldcg(W.w + i))) W.w[i] = 0;
     }
   }
   if (wid == 0 && n_steps > 0) fused_plan(plans[0], blk_tab, order, 0, bps);
@@ -1173,12 +1143,8 @@ __device__ __forceinline__ void darlin_pass_body(
     const uint64_t seq = seq_base + (uint64_t)step + 1;
     const bool has_next = step + 1 < n_steps;
     Carry C0;
-    // ---- phase 1: gradient + push ----
-    {
-      const double vio = grad_phase_packed<BINARY, SINGLE>(W, S, h, P.wk, bps, gw, nw, lane, pre, exp_tab,
-                                                           (uint32_t)seq, C0);
-      if (SINGLE && vio > 0) atomic_max_nonneg(S.violation, vio);
-    }
+    // ---- phase 1: gradient, then accumulate (one rank) or push (several) ----
+    grad_phase_packed<BINARY, SINGLE>(W, S, h, P.wk, bps, gw, nw, lane, pre, exp_tab, (uint32_t)seq, C0);
     if (prof && threadIdx.x == 0) {  // per-step straggler: max phase-1 time and its CTA
       unsigned long long now_;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
@@ -1189,17 +1155,16 @@ __device__ __forceinline__ void darlin_pass_body(
     // Several ranks: the pushes are in flight meanwhile.
     grid_arrive_by(bar, kSpinner);
     if (wid == 1 && step + 2 < n_steps) fused_plan(plans[(step + 2) % 3], blk_tab, order, step + 2, bps);
-    if (has_next && do_prefetch && wid != kWarps - 1) prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
+    int4 next_meta = make_int4(0, -1, 0, 0);
+    if (has_next && do_prefetch && wid != kWarps - 1) next_meta = prefetch_step<BINARY>(W, Pn.wk, bps, gw, nw, lane);
     PSB_PROF(1)
     grid_wait_by(bar, (uint32_t)(step + 1) * G, kSpinner);
     PSB_PROF(2)
     // ---- phase 3: (several ranks: collect the entries, update the replica) margins ----
     {
       double vio = pull_phase_packed<BINARY, SINGLE>(W, S, h, P.wk, bps, gw, nw, lane, pre, (uint32_t)seq, C0);
-      if (!SINGLE) {
-        vio = warp_max(vio);
-        if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
-      }
+      vio = warp_max(vio);
+      if (lane == 0 && vio > 0) atomic_max_nonneg(S.violation, vio);
     }
     if (prof && threadIdx.x == 0) {
       unsigned long long now_;
@@ -1208,10 +1173,14 @@ __device__ __forceinline__ void darlin_pass_body(
     }
     PSB_PROF(3)
     grid_arrive_by(bar + 2, kSpinner);
+    const bool first_known = pre.v == gw;
+    const int64_t first_j = (first_known && pre.first) ? pre.j : -1;
     pre.v = -1;
-    if (has_next && wid != kWarps - 1 && gw < Pn.wk.pref[bps]) stage_segment<BINARY, SINGLE>(pre, W, Pn.wk, bps, gw, lane);
+    if (has_next && wid != kWarps - 1 && gw < Pn.wk.pref[bps])
+      stage_segment<BINARY, SINGLE>(pre, W, Pn.wk, bps, gw, lane, next_meta);
     if (SINGLE) {
       grid_wait_by(bar + 2, (uint32_t)(step + 1) * G, kSpinner);
+      clear_accumulators(W, P.wk, bps, gw, nw, lane, first_j, first_known, (uint32_t)seq);
     } else {
       grid_wait_flow(bar + 2, (uint32_t)(step + 1) * G, W.done_local, W.n_workers, seq + 1);
       // this rank has consumed every entry of the step: tell the peers (plain stores, the reads

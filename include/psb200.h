@@ -103,6 +103,8 @@ typedef struct psb_darlin_worker {
   uint64_t* done_peer[PSB_MAX_PEERS];
   int32_t push_fp32;   /* 1: (g, u) are pushed rounded to fp32 in one 16-byte store (lossy push filter) */
   int32_t reserved1;
+  double* acc;         /* fused one-rank pass: [2 parities][n_cols][2] accumulators of (g, u), all zero
+                          between launches */
 } psb_darlin_worker;
 
 /* Server side: one key-range shard of the model. */
@@ -188,8 +190,9 @@ int psb_darlin_evaluate_noalloc(const psb_darlin_worker* wk, const psb_darlin_se
                                 uint64_t seq, int32_t grid, void* stream);
 
 /* Whole pass in ONE cooperative launch: pass_begin, every step and the evaluation run inside
- * a persistent kernel whose phases are separated by grid barriers; with one rank the shard
- * update is applied by the warp that completes a column's gradient.  `bar`: 4 zeroed uint32
+ * a persistent kernel whose phases are separated by grid barriers; with one rank the segments
+ * accumulate (g, u) into worker.acc with fp64 reductions and every segment applies the column's
+ * update itself after the barrier (worker.w is the replica of the shard, NaN-marked like it).  `bar`: 4 zeroed uint32
  * owned by the caller.  blk_tab[b] = {first segment, #segments, first shard key, #shard keys,
  * server mask, 0}.  grid <= psb_darlin_fused_max_grid().  prof (optional): 5 uint64 that
  * accumulate ns spent in {phase 1, plan+prefetch, barrier A wait, phase 3, barrier C}. */

@@ -374,6 +374,7 @@ class DarlinEngine:
         self.wk_active = _full_bitmap(self.n_cols, dev)
         self.part = torch.zeros(2 * self.bps * max(self.max_blk_segs, 1), **f64)
         self.stash = torch.zeros(2 * self.bps * max(self.max_blk_segs, 1), **f64)
+        self.acc = torch.zeros(4 * max(self.n_cols, 1), **f64)   # one-rank pass: (g, u) accumulators, 2 parities
         self.col_cnt = torch.zeros(max(self.n_cols, 1), dtype=torch.int32, device=dev)
         self.ctrs = torch.zeros(16, dtype=torch.int32, device=dev)
         sm = torch.cuda.get_device_properties(dev).multi_processor_count
@@ -422,6 +423,7 @@ class DarlinEngine:
         wk.col_has, wk.stash = self.col_has.data_ptr(), self.stash.data_ptr()
         wk.done_local = self.b_done.ptr
         wk.push_fp32 = int(cfg.push_format == "fp32")
+        wk.acc = self.acc.data_ptr()
         for s in range(W):
             wk.land2[s] = A.peer_ptr(s, self.b_land2)
             wk.done_peer[s] = A.peer_ptr(s, self.b_done, self.rank)
@@ -602,7 +604,7 @@ class DarlinEngine:
         self.comm.barrier()
         self.b_w.tensor.zero_(); self.b_dw.tensor.zero_()
         self.b_land_g.tensor.zero_(); self.b_land_u.tensor.zero_()
-        self.z.zero_(); self.w_cache.zero_(); self.violation.zero_()
+        self.z.zero_(); self.w_cache.zero_(); self.violation.zero_(); self.acc.zero_()
         self.srv_delta.fill_(self.cfg.delta_init_value)
         self.wk_delta.fill_(self.cfg.delta_init_value)
         self.srv_active.copy_(_full_bitmap(self.n_keys, self.device))

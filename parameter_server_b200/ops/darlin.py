@@ -35,7 +35,7 @@ class DarlinWorker(C.Structure):
                 ("srv_w", P * MAX_PEERS), ("srv_dw", P * MAX_PEERS), ("ver_flag", P),
                 ("seg_meta", P), ("land2", P * MAX_PEERS), ("col_has", P), ("stash", P),
                 ("done_local", P), ("done_peer", P * MAX_PEERS), ("push_fp32", C.c_int32),
-                ("reserved1", C.c_int32)]
+                ("reserved1", C.c_int32), ("acc", P)]
 
 
 class DarlinServer(C.Structure):
