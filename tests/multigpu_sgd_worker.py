@@ -97,7 +97,8 @@ def main():
                                        for d, k in diffs[:6]]}
                 gap = max(abs(a - b) for a, b in zip(traj, rtraj))
                 out["tau0"]["max_loss_gap"] = gap
-                out["ok"] &= (traj[0] == rtraj[0] and gap < 5e-3 and err < 0.1 and len(multi) > 100
+                # (even the first step may see part of the other worker's push: no exact equality anywhere)
+                out["ok"] &= (gap < 5e-3 and err < 0.1 and len(multi) > 100
                               and abs(len(multi) - len(ref)) <= 20 and sum(dups) == 0)
             else:
                 out["tau2"] = {"nnz": len(multi), "mean_loss": loss[0] / max(loss[2], 1)}
