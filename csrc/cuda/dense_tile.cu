@@ -9,17 +9,19 @@
 // src/data/text_parser.cc:27,200-250) are the only dense matrices the reference knows; its own
 // path for them is the generic SpMV (src/util/sparse_matrix.h:72-124).
 //
-// Structure (one CTA per 128-row tile, 256 threads, no cluster, no multicast):
+// Structure (persistent CTAs over 128-row tiles, 384 threads, no cluster, no multicast):
 //   warp 0   TMA producer: cp.async.bulk.tensor loads of the A tile (128 x 64 bf16) and the B
 //            tile (N x 64 bf16) into a 4-stage shared-memory ring, 128-byte swizzle; both tensor
 //            maps describe buffers of THIS GPU only
 //   warp 1   MMA issuer: one elected lane issues tcgen05.mma (cta_group::1, kind::f16, M=128,
 //            N=Npad, K=16) four times per stage, commits the stage back to the producer and, after
 //            the last k-block, the accumulator to the epilogue
-//   warp 2   allocates / frees the TMEM columns of the accumulator
-//   warps 4-7 epilogue: tcgen05.ld (32 lanes x 32 bit, 16 columns at a time) -> registers ->
-//            margins to global memory + per-model logistic loss (warp shuffle + one atomic per
-//            warp and model)
+//   warp 2   allocates / frees the TMEM columns of the two accumulators
+//   warps 4-11 epilogue (two per TMEM lane quarter): tcgen05.ld (32 lanes x 32 bit, 16 columns at a time) -> registers ->
+//            margins to global memory (128-bit stores) + per-model logistic loss (transposing
+//            warp reduction into shared memory, one atomic per CTA and model at the very end)
+// The kernel is persistent and the accumulator double-buffered, so the epilogue of one row tile
+// overlaps the loads and MMAs of the next.
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -29,7 +31,7 @@
 namespace psb {
 
 constexpr int kTileM = 128, kTileK = 64, kStages = 4, kUmmaK = 16;
-constexpr int kDenseThreads = 256;
+constexpr int kDenseThreads = 384;  // 4 service warps + 8 epilogue warps
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -73,6 +75,13 @@ __device__ __forceinline__ uint32_t instr_desc_bf16(int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
 }
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Persistent: CTA c works on row tiles c, c + grid, ...  The smem ring runs across tile
+// boundaries, and the accumulator is double-buffered in TMEM (2 x NPAD columns) so that the
+// epilogue of tile i overlaps the loads and MMAs of tile i + 1.
 template <int NPAD>
 __global__ void __launch_bounds__(kDenseThreads, 1)
 k_dense_margins(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
@@ -86,86 +95,154 @@ k_dense_margins(const __grid_constant__ CUtensorMap map_x, const __grid_constant
   unsigned char* tile_b = base + kStages * kBytesA;
   uint64_t* full = reinterpret_cast<uint64_t*>(tile_b + kStages * kBytesB);
   uint64_t* empty = full + kStages;
-  uint64_t* acc_full = empty + kStages;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+  uint64_t* acc_full = empty + kStages;   // [2]
+  uint64_t* acc_empty = acc_full + 2;     // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  float* loss_s = reinterpret_cast<float*>(tmem_slot + 4);  // [4 epilogue warps][NPAD]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * kTileM;
   const int k_blocks = (d + kTileK - 1) / kTileK;
-  constexpr uint32_t kTmemCols = NPAD < 32 ? 32 : NPAD;  // power of two >= 32 (NPAD is 16, 32, 64, 128 or 256)
+  const int n_tiles = (n + kTileM - 1) / kTileM;
+  constexpr uint32_t kTmemCols = 2 * NPAD < 32 ? 32 : 2 * NPAD;  // two accumulators, a power of two >= 32
 
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
-    mbar_init(acc_full, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(acc_full + s, 1); mbar_init(acc_empty + s, 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   } else if (warp == 2) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(kTmemCols));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
+  for (int i = threadIdx.x; i < 4 * NPAD; i += kDenseThreads) loss_s[i] = 0.f;
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tmem_acc = *tmem_slot;
+  const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0 && lane == 0) {
     // ---- TMA producer ----
-    for (int kb = 0; kb < k_blocks; ++kb) {
-      const int s = kb % kStages;
-      if (kb >= kStages) mbar_wait(empty + s, ((kb / kStages) - 1) & 1);
-      mbar_expect_tx(full + s, kBytesA + kBytesB);
-      tma_load_2d(tile_a + s * kBytesA, &map_x, full + s, kb * kTileK, m0);  // rows past n / columns past d read as 0
-      tma_load_2d(tile_b + s * kBytesB, &map_w, full + s, kb * kTileK, 0);
-    }
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
+      for (int kb = 0; kb < k_blocks; ++kb, ++it) {
+        const int s = it % kStages;
+        if (it >= kStages) mbar_wait(empty + s, ((it / kStages) - 1) & 1);
+        mbar_expect_tx(full + s, kBytesA + kBytesB);
+        tma_load_2d(tile_a + s * kBytesA, &map_x, full + s, kb * kTileK, tile * kTileM);  // rows past n / columns past d read as 0
+        tma_load_2d(tile_b + s * kBytesB, &map_w, full + s, kb * kTileK, 0);
+      }
   } else if (warp == 1 && lane == 0) {
     // ---- MMA issuer ----
     const uint32_t idesc = instr_desc_bf16(NPAD);
-    for (int kb = 0; kb < k_blocks; ++kb) {
-      const int s = kb % kStages;
-      mbar_wait(full + s, (kb / kStages) & 1);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint64_t da = smem_desc_sw128(tile_a + s * kBytesA), db = smem_desc_sw128(tile_b + s * kBytesB);
+    int it = 0, i = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
+      const int as = i & 1;
+      if (i >= 2) {  // the epilogue has drained this accumulator
+        mbar_wait(acc_empty + as, ((i >> 1) - 1) & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      }
+      const uint32_t tmem_acc = tmem_base + (uint32_t)(as * NPAD);
+      for (int kb = 0; kb < k_blocks; ++kb, ++it) {
+        const int s = it % kStages;
+        mbar_wait(full + s, (it / kStages) & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint64_t da = smem_desc_sw128(tile_a + s * kBytesA), db = smem_desc_sw128(tile_b + s * kBytesB);
 #pragma unroll
-      for (int k = 0; k < kTileK / kUmmaK; ++k)  // 16 bf16 = 32 bytes = 2 descriptor units along the swizzled row
-        umma_bf16(tmem_acc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-      umma_commit(empty + s);               // the stage may be refilled once these MMAs have read it
-      if (kb == k_blocks - 1) umma_commit(acc_full);
+        for (int k = 0; k < kTileK / kUmmaK; ++k)  // 16 bf16 = 32 bytes = 2 descriptor units along the swizzled row
+          umma_bf16(tmem_acc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+        umma_commit(empty + s);               // the stage may be refilled once these MMAs have read it
+      }
+      umma_commit(acc_full + as);
     }
   } else if (warp >= 4) {
     // ---- epilogue: this warp owns TMEM lanes [32 * (warp % 4), +32) = rows of the tile ----
-    mbar_wait(acc_full, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const int quarter = warp & 3;
-    const int row = m0 + quarter * 32 + lane;
-    const float yl = row < n ? label[row] : 0.f;
+    // two warps per lane quarter: they split the 16-column chunks between them
+    const int quarter = warp & 3, half = (warp - 4) >> 2;
+    float* my_loss = loss_s + quarter * NPAD;
+    const bool vec = (n_models & 3) == 0;
+    int i = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
+      const int as = i & 1;
+      mbar_wait(acc_full + as, (i >> 1) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const int row = tile * kTileM + quarter * 32 + lane;
+      const float yl = row < n ? label[row] : 0.f;
 #pragma unroll
-    for (int c0 = 0; c0 < NPAD; c0 += 16) {
-      uint32_t v[16];
-      const uint32_t taddr = tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0;
-      asm volatile(
-          "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-            "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-          : "r"(taddr));
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      for (int c0 = half * 16; c0 < NPAD; c0 += 32) {
+        if (c0 >= n_models) break;  // uniform
+        uint32_t v[16];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * NPAD + c0);
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+            : "r"(taddr));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        // margins: 16 consecutive floats of this thread's row
+        if (Y && row < n) {
+          float* dst = Y + (int64_t)row * n_models + c0;
+          if (vec && c0 + 16 <= n_models) {
 #pragma unroll
-      for (int c = 0; c < 16; ++c) {
-        const int model = c0 + c;
-        if (model >= n_models) break;                      // uniform over the warp
-        const float m = __uint_as_float(v[c]);
-        float l = 0.f;
-        if (row < n) {
-          Y[(int64_t)row * n_models + model] = m;
-          const float ym = yl * m;                         // log(1 + exp(-y m)) without overflow
-          l = ym > 0 ? log1pf(__expf(-ym)) : (-ym + log1pf(__expf(ym)));
+            for (int q = 0; q < 4; ++q)
+              *reinterpret_cast<float4*>(dst + 4 * q) = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
+                                                                     __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
+          } else {
+#pragma unroll
+            for (int c = 0; c < 16; ++c)
+              if (c0 + c < n_models) dst[c] = __uint_as_float(v[c]);
+          }
         }
-        l = warp_sum(l);
-        if (lane == 0 && loss) atomicAdd(loss + model, (double)l);
+        if (loss) {
+          // log(1 + exp(-y m)) without overflow; rows past n contribute 0
+          float l[16];
+#pragma unroll
+          for (int c = 0; c < 16; ++c) {
+            const float ym = yl * __uint_as_float(v[c]);
+            l[c] = row < n ? fmaxf(-ym, 0.f) + __logf(1.f + __expf(-fabsf(ym))) : 0.f;
+          }
+          // sum over the 32 rows of the warp for 16 models at once: halve the model set while
+          // folding lanes (16 + 8 + 4 + 2 + 1 shuffles instead of 16 x 5)
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const float send = (lane & 16) ? l[c] : l[c + 8];
+            const float keep = (lane & 16) ? l[c + 8] : l[c];
+            l[c] = keep + __shfl_xor_sync(FULL, send, 16);
+          }
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const float send = (lane & 8) ? l[c] : l[c + 4];
+            const float keep = (lane & 8) ? l[c + 4] : l[c];
+            l[c] = keep + __shfl_xor_sync(FULL, send, 8);
+          }
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            const float send = (lane & 4) ? l[c] : l[c + 2];
+            const float keep = (lane & 4) ? l[c + 2] : l[c];
+            l[c] = keep + __shfl_xor_sync(FULL, send, 4);
+          }
+          {
+            const float send = (lane & 2) ? l[0] : l[1];
+            const float keep = (lane & 2) ? l[1] : l[0];
+            l[0] = keep + __shfl_xor_sync(FULL, send, 2);
+          }
+          l[0] += __shfl_xor_sync(FULL, l[0], 1);
+          // lane L now holds the sum of model c0 + 8*b4 + 4*b3 + 2*b2 + b1 (bits of L), twice (b0)
+          if (!(lane & 1)) {
+            const int model = c0 + ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+            my_loss[model] += l[0];  // one lane per model and warp: no atomics
+          }
+        }
       }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty + as);
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
-  if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "n"(kTmemCols));
+  if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols));
+  if (loss)
+    for (int m = threadIdx.x; m < n_models; m += kDenseThreads)
+      atomicAdd(loss + m, (double)loss_s[m] + (double)loss_s[NPAD + m] + (double)loss_s[2 * NPAD + m] + (double)loss_s[3 * NPAD + m]);
 }
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point: no link-time dependency on libcuda
@@ -199,9 +276,18 @@ static int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t col
 template <int NPAD>
 static int launch_dense(const CUtensorMap& mx, const CUtensorMap& mw, float* Y, const float* label, double* loss,
                         int n, int d, int n_models, cudaStream_t stream) {
-  const size_t smem = 1024 + kStages * (kTileM * kTileK * 2 + NPAD * kTileK * 2) + (2 * kStages + 1) * 8 + 16;
+  const size_t smem = 1024 + kStages * (kTileM * kTileK * 2 + NPAD * kTileK * 2) + (2 * kStages + 4) * 8 + 16 + 4 * NPAD * 4;
   PSB_CUDA(cudaFuncSetAttribute(k_dense_margins<NPAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  k_dense_margins<NPAD><<<(n + kTileM - 1) / kTileM, kDenseThreads, smem, stream>>>(mx, mw, Y, label, loss, n, d, n_models);
+  const int tiles = (n + kTileM - 1) / kTileM;
+  // persistent: as many CTAs as fit (shared memory bound), each walking tiles with stride grid
+  int per_sm = 1;
+  PSB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dense_margins<NPAD>, kDenseThreads, smem));
+  // every resident CTA holds 2 * NPAD TMEM columns of the 512 of its SM
+  const int tmem_fit = 512 / (2 * NPAD < 32 ? 32 : 2 * NPAD);
+  if (per_sm > tmem_fit) per_sm = tmem_fit;
+  if (per_sm < 1) per_sm = 1;
+  const int grid = tiles < per_sm * sm_count() ? tiles : per_sm * sm_count();
+  k_dense_margins<NPAD><<<grid, kDenseThreads, smem, stream>>>(mx, mw, Y, label, loss, n, d, n_models);
   PSB_LAUNCH_CHECK();
   return 0;
 }
@@ -212,12 +298,12 @@ using namespace psb;
 
 // Y[n x n_models] (fp32) = X[n x d] * W[n_models x d]^T with bf16 operands (ld = elements per row,
 // multiples of 8; 16-byte aligned pointers); loss[m] += sum_i log(1 + exp(-label_i * Y[i][m])) when
-// loss != NULL (zero it first).  n_models <= 256.  X, W, Y, label, loss are buffers of the current
+// loss != NULL (zero it first); Y may be NULL when only the losses are wanted.  n_models <= 256.  X, W, Y, label, loss are buffers of the current
 // device; the tensor maps built here never describe another GPU's memory.
 PSB_API int psb_dense_margins_bf16(const void* X, int64_t ldx, const void* W, int64_t ldw, float* Y,
                                    const float* label, double* loss, int32_t n, int32_t d, int32_t n_models,
                                    void* stream) {
-  PSB_REQUIRE(X && W && Y && label && n >= 1 && d >= 1, "psb_dense_margins_bf16: bad argument");
+  PSB_REQUIRE(X && W && label && (Y || loss) && n >= 1 && d >= 1, "psb_dense_margins_bf16: bad argument");
   PSB_REQUIRE(n_models >= 1 && n_models <= 256, "psb_dense_margins_bf16: n_models=%d outside [1,256]", n_models);
   PSB_REQUIRE(ldx % 8 == 0 && ldw % 8 == 0 && ldx >= d && ldw >= d, "psb_dense_margins_bf16: leading dimensions must be multiples of 8 and >= d");
   int npad = 16;

@@ -31,7 +31,7 @@ def pad_features(x: torch.Tensor) -> torch.Tensor:
 
 
 def dense_margins(x: torch.Tensor, w: torch.Tensor, label: torch.Tensor, d: int | None = None,
-                  with_loss: bool = True):
+                  with_loss: bool = True, with_margins: bool = True):
     """x: [n, ld] bf16, w: [K, ld'] bf16 (row strides multiples of 8), label: [n] float32 (+-1).
     Returns (Y [n, K] float32, loss [K] float64 or None): Y = x[:, :d] @ w[:, :d].T,
     loss[k] = sum_i log(1 + exp(-label_i Y[i, k]))."""
@@ -39,7 +39,7 @@ def dense_margins(x: torch.Tensor, w: torch.Tensor, label: torch.Tensor, d: int 
     assert x.stride(1) == 1 and w.stride(1) == 1
     n, k = x.shape[0], w.shape[0]
     d = d if d is not None else min(x.shape[1], w.shape[1])
-    y = torch.empty(n, k, dtype=torch.float32, device=x.device)
+    y = torch.empty(n, k, dtype=torch.float32, device=x.device) if with_margins else None
     loss = torch.zeros(k, dtype=torch.float64, device=x.device) if with_loss else None
     check(_lib().psb_dense_margins_bf16(ptr(x), x.stride(0), ptr(w), w.stride(0), ptr(y),
                                         ptr(label.float().contiguous()), ptr(loss), n, d, k, current_stream()))
