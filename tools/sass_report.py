@@ -18,12 +18,15 @@ KERNELS = {
     "k_sgd_worker_step": "k_sgd_worker_step.sass",
     "k_sgd_server_all": "k_sgd_server_all.sass",
     "k_sgd_serverE": "k_sgd_server.sass",
-    "k_kv_bulk_send": "k_kv_bulk_send.sass",
+    "k_kv_bulk_pull_apply": "k_kv_bulk_pull_apply.sass",
+    "k_kv_bulk_gather_send32": "k_kv_bulk_gather_send32.sass",
     "k_kv_push_add": "k_kv_push_add.sass",
+    "k_dense_marginsILi64": "k_dense_margins_n64.sass",
+    "k_dkv_applyId": "k_dkv_apply_f64.sass",
 }
 INTEREST = re.compile(r"\b(ATOMG|ATOM|REDG|RED|MEMBAR|ERRBAR|CGAERRBAR|CCTL|LDG\.E[\w.]*STRONG[\w.]*|"
                       r"STG\.E[\w.]*STRONG[\w.]*|LDG\.E\.128[\w.]*|STG\.E\.128[\w.]*|DFMA|DADD|DMUL|MUFU[\w.]*|"
-                      r"UTCMMA|UTMALDG|UBLKCP|HMMA|SHFL\.\w+)[\w.]*")
+                      r"UTC\w*MMA|UTMALDG|UBLKCP|UTCBAR|LDTM|STTM|SYNCS|HMMA|SHFL\.\w+)[\w.]*")
 
 
 def main() -> int:
@@ -33,11 +36,13 @@ def main() -> int:
     lines = ["# SASS evidence (cuobjdump -sass libpsb200_cuda.so, sm_100a)",
              "Regenerate with `python tools/sass_report.py`.  Counts of the instructions that implement the",
              "fused compute+communication protocol: `*.STRONG.SYS` = system-scope acquire/release or volatile",
-             "traffic on peer-visible memory (landing slots, mirrors, flags), `RED`/`ATOM` = reductions / atomics",
+             "traffic on peer-visible memory (tagged landing entries, flags), `RED`/`ATOM` = reductions / atomics",
              "(margin scatter, counters, CAS inserts), `MEMBAR.*.SYS` + `ERRBAR` = fences before cross-GPU",
              "stores, `.STRONG.GPU` = grid-barrier traffic, `CCTL.IVALL` = L1 invalidation after an acquire,",
              "`DFMA`/`MUFU.RCP64H` = the fp64 exp / reciprocal of the logistic gradient.",
-             "No tensor-core instruction is expected: the workload is sparse (SpMV-class), see DESIGN.md.", ""]
+             "The sparse kernels carry no tensor-core instruction (SpMV-class work, see DESIGN.md); the dense",
+             "feature-block tile does: `UTCHMMA` = tcgen05.mma, `UTMALDG` = TMA tensor load, `LDTM` = tcgen05.ld,",
+             "`UTCBAR` = tcgen05.commit, `SYNCS` = mbarrier operations.", ""]
     for f in funcs:
         name = f.split("\n", 1)[0].strip()
         for key, fn in KERNELS.items():
