@@ -303,8 +303,10 @@ class DarlinWorker : public BCDWorker<Real> {
   // a block on the worker: push (G, U) at `time`, then pull the new weights behind the server's
   // "updated" mark; the scheduler's task is finished by the pull's callback.  ref darlin.h:297-342
   void computeGradient(int time, const BCDCallView& call, MessagePtr task) override {
-    if (call.reset_kkt_filter())
+    if (call.reset_kkt_filter()) {
+      Lock l(mu_);  // pulls of the previous pass' last blocks may still be landing (tau > 0)
       for (int g : fea_grp_) state_[g].active.fill(true);
+    }
     CHECK_EQ(call.fea_grp_size(), 1);
     const int grp = call.fea_grp(0);
     const Range<Key> block = call.key().to<Key>();
@@ -358,6 +360,10 @@ class DarlinWorker : public BCDWorker<Real> {
 
   // ref darlin.h:429-502: a NaN weight means "the server filtered this coordinate"
   void adoptWeights(int grp, SizeR cols, const SArray<Real>& fresh) {
+    const auto X = matrix(grp);
+    // the active bitmap shares words with the columns of other blocks, which a gradient task of
+    // the app executor may be reading (tau > 0): the whole update runs under the lock
+    Lock l(mu_);
     CoordinateState& st = state_[grp];
     SArray<Real>& w = model_.value(grp);
     const Real delta_max = bcd_conf_.delta_max_value();
@@ -373,8 +379,6 @@ class DarlinWorker : public BCDWorker<Real> {
       st.delta[j] = DarlinMath::trustRegion(delta_max, dw[i]);
       w[j] = fresh[i];
     }
-    const auto X = matrix(grp);
-    Lock l(mu_);
     busy_.start();
     const int threads = std::max(1, (int)FLAGS_num_threads);
     const SizeR rows(0, X->rows());
