@@ -8,8 +8,9 @@ max_delay 4, tail_feature_freq 1, lambda (10, 1), DECAY alpha .01 beta 10), at t
 
 The examples live in PINNED HOST memory (what the reference's StreamReader + prefetch queue hold,
 src/learner/sgd.h:104-157); every pass streams them again: one async H2D copy per array and
-minibatch, localisation (sort / unique / CountMin tail filter / remap / table slots) on a side
-stream by the prefetch thread, then per step the fused worker kernel (pull over NVLink -> margins,
+minibatch into a ring of device buffers, localisation (sort / unique / CountMin tail filter / remap
+/ table slots; one enqueue, no host sync) on the copy stream, all issued by the native runner
+(csrc/cuda/sgd_stream.cu), then per step the fused worker kernel (pull over NVLink -> margins,
 loss, gradient -> push, fp32 / int8 / fp8) and the owner's apply.  Nothing is cached: the first
 pass and the later ones do the same work, except that later passes find their keys in the tables.
 Timed from the first minibatch of the first pass with CUDA events + wall clock, max over ranks.
@@ -186,9 +187,16 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot)
         dist.all_reduce(load, op=dist.ReduceOp.MAX)
-    if eng._stage_prof is not None:
-        print(f"rank {rank}: prefetch busy {eng.prefetch_busy_s:.2f}s, step loop waited {eng.feed_wait_s:.2f}s, stages "
-              + str({k: round(v, 3) for k, v in eng._stage_prof.items()}), file=sys.stderr, flush=True)
+    if os.environ.get("PSB_SGD_TIMING") and eng._runner is not None:
+        print(f"rank {rank}: stage ms/step {eng._runner.timing()}", file=sys.stderr, flush=True)
+    if os.environ.get("PSB_LOC_TIMING"):
+        import ctypes
+        out7 = (ctypes.c_double * 7)()
+        eng.lib.psb_sgd_localize_timing.restype = ctypes.c_int64
+        calls = eng.lib.psb_sgd_localize_timing(out7)
+        names = ("sort", "rle", "sketch", "select", "columns", "owner_begin", "slots")
+        print(f"rank {rank}: localise ms/call over {calls} calls "
+              + str({k: round(v, 4) for k, v in zip(names, out7)}), file=sys.stderr, flush=True)
     if rank == 0:
         ms, wall_ms, first_ms, steady_ms = t.tolist()
         ex_pass = tot[0].item() / args.passes
@@ -207,7 +215,7 @@ def main():
                        "first_pass_examples_per_s": ex_pass / (first_ms / 1e3),
                        "steady_examples_per_s": ex_pass / (steady_ms / 1e3) if args.passes > 1 else None,
                        "per_pass": per_pass, "generate_s": t_gen,
-                       "rank0_prefetch_busy_s": eng.prefetch_busy_s, "rank0_step_loop_waited_s": eng.feed_wait_s,
+                       "rank0_host_enqueue_s": eng.submit_s, "rank0_host_source_s": eng.source_s,
                        "host_cpus": os.cpu_count(),
                        "timing": "CUDA events from the first minibatch of pass 0 (nothing cached or warmed), max over ranks"},
             "e2e": {"value": tot[0].item() / (wall_ms / 1e3), "unit": "examples/s",

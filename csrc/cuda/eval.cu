@@ -7,6 +7,7 @@
 //      src/util/shared_array_inl.h:103-130, src/util/bitmap.h:35-75,
 //      src/util/sparse_matrix.h:72-86, src/app/linear_method/model_evaluation.h:40-66
 #include "common.cuh"
+#include "sketch.cuh"
 #include "../../include/psb200.h"
 #include <cub/cub.cuh>
 
@@ -54,26 +55,6 @@ __global__ void k_acc_logloss(const float* __restrict__ label, const float* __re
 }
 
 // ---- K13 ----------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t sketch_hash(uint64_t key) {  // == PS::Sketch::hash on the host
-  const uint32_t m = 0xc6a4a793u;
-  uint32_t h = 0xbc9f1d34u ^ (8u * m);
-  h += (uint32_t)key; h *= m; h ^= h >> 16;
-  h += (uint32_t)(key >> 32); h *= m; h ^= h >> 16;
-  return h;
-}
-// saturating add of `count` to byte `pos` of a uint8 table, via CAS on the containing word
-__device__ __forceinline__ void sat_add_u8(uint8_t* table, uint32_t pos, uint32_t count, uint32_t vmax) {
-  uint32_t* word = reinterpret_cast<uint32_t*>(table) + (pos >> 2);
-  const int shift = (pos & 3) * 8;
-  uint32_t old = *word, assumed;
-  do {
-    assumed = old;
-    const uint32_t cur = (assumed >> shift) & 0xffu;
-    const uint32_t nv = count > vmax - cur ? vmax : cur + count;
-    if (nv == cur) return;
-    old = atomicCAS(word, assumed, (assumed & ~(0xffu << shift)) | (nv << shift));
-  } while (old != assumed);
-}
 __global__ void k_countmin_insert(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ counts,
                                   int64_t n, uint8_t* table, uint32_t cm_n, int cm_k, uint32_t vmax) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;

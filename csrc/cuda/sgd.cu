@@ -29,6 +29,7 @@ constexpr int kSgdThreads = 256;
 constexpr int kSgdWarps = kSgdThreads / 32;
 constexpr uint64_t kEmptyKey = ~0ULL;
 constexpr int kQuantBlock = 128;
+constexpr uint32_t kFilteredColumn = 0xffffffffu;  // col entry of a key the tail filter dropped (sgd_localize.cu)
 
 __device__ __forceinline__ uint64_t hash_key(uint64_t x) {
   x ^= x >> 33; x *= 0xff51afd7ed558ccdULL;
@@ -133,7 +134,8 @@ k_sgd_worker_step(const __grid_constant__ SgdWorker W, uint64_t seq, uint32_t* b
   }
 
   // ---- phase 1: pull the weights of this minibatch's columns from their owners ----
-  for (int64_t j = gt; j < W.n_cols; j += nt) {
+  const int64_t n_cols = W.n_cols_dev ? *W.n_cols_dev : W.n_cols;
+  for (int64_t j = gt; j < n_cols; j += nt) {
     const int64_t s = W.col_slot[j];
     float w = 0.f;
     if (s >= 0) w = *reinterpret_cast<const volatile float*>(W.tab_w[W.col_owner[j]] + s);
@@ -149,7 +151,9 @@ k_sgd_worker_step(const __grid_constant__ SgdWorker W, uint64_t seq, uint32_t* b
     const int64_t b = W.row_ptr[r], e = W.row_ptr[r + 1];
     float m = 0.f;
     for (int64_t k = b + lane; k < e; k += 32) {
-      const float wv = __ldcg(W.w_local + W.col[k]);
+      const uint32_t c = W.col[k];
+      if (c == kFilteredColumn) continue;
+      const float wv = __ldcg(W.w_local + c);
       m += W.val ? wv * W.val[k] : wv;
     }
     m = warp_sum(m);
@@ -162,8 +166,10 @@ k_sgd_worker_step(const __grid_constant__ SgdWorker W, uint64_t seq, uint32_t* b
       correct += ((yr > 0 && m > 0) || (yr < 0 && m <= 0)) ? 1.0 : 0.0;
     }
     if (res != 0.f)
-      for (int64_t k = b + lane; k < e; k += 32)
-        atomicAdd(W.g_local + W.col[k], W.val ? res * W.val[k] : res);
+      for (int64_t k = b + lane; k < e; k += 32) {
+        const uint32_t c = W.col[k];
+        if (c != kFilteredColumn) atomicAdd(W.g_local + c, W.val ? res * W.val[k] : res);
+      }
   }
   if (lane == 0 && (loss_acc != 0 || correct != 0)) {
     atomicAdd(W.stats, loss_acc);
@@ -177,7 +183,7 @@ k_sgd_worker_step(const __grid_constant__ SgdWorker W, uint64_t seq, uint32_t* b
   const int64_t sblk = W.land_cap / kQuantBlock + 1;
   for (int s = 0; s < W.n_servers; ++s) {
     const int64_t lo = W.owner_begin[s], hi = W.owner_begin[s + 1];
-    const int64_t n = hi - lo;
+    const int64_t n = min(hi - lo, W.land_cap);  // a longer segment was reported by the localisation
     int32_t* d_slot = W.land_slot[s] + region * W.land_cap;
     if (W.quant == 0) {
       float* d_val = W.land_val[s] + region * W.land_cap;
@@ -225,7 +231,7 @@ k_sgd_worker_step(const __grid_constant__ SgdWorker W, uint64_t seq, uint32_t* b
   grid_wait(bar, 3 * G);
   if (threadIdx.x < W.n_servers) {
     const int s = threadIdx.x;
-    W.land_cnt[s][region] = W.owner_begin[s + 1] - W.owner_begin[s];
+    W.land_cnt[s][region] = min(W.owner_begin[s + 1] - W.owner_begin[s], W.land_cap);
     __threadfence_system();
     st_release_sys(W.land_flag[s], seq);
   }

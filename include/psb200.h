@@ -265,6 +265,9 @@ typedef struct psb_sgd_worker {
   int32_t rank, n_workers, n_servers, depth;
   int32_t loss;    /* LossConfig::Type: 1 SQUARE, 2 LOGIT, 4 SQUARE_HINGE */
   int32_t quant;   /* 0: fp32 push; 1: int8, 2: fp8 e4m3, both with one fp32 scale per 128 values */
+  const int64_t* n_cols_dev;  /* not NULL: the column count is read from here (minibatches localised by
+                                 psb_sgd_localize, whose sizes never reach the host); n_cols is then only
+                                 an upper bound, and col may hold 0xffffffff = filtered key, skipped */
 } psb_sgd_worker;
 
 typedef struct psb_sgd_server {
@@ -295,6 +298,22 @@ int psb_kv_table_clear(uint64_t* keys, int64_t cap, void* stream);
 int psb_kv_lookup_insert(const uint64_t* keys, int64_t n, const int32_t* owner,
                          uint64_t* const* table_keys_host, const int64_t* cap_host, int32_t n_servers,
                          int64_t* slot_out, int32_t* overflow_dev, void* stream);
+/* Whole minibatch localisation as one enqueue without a host synchronisation (sgd_localize.cu):
+ * sort + run-length -> CountMin tail filter (sketch == NULL: none) -> kept keys `cols` -> local
+ * column of every non-zero (`col`, 0xffffffff for a filtered key) -> owner segments -> table slots.
+ * Device buffers of capacity nnz: sorted, uniq, cnt, flag, cols, col, col_owner, col_slot;
+ * counts_dev[2] <- {unique keys, kept keys}; owner_begin[n_servers+1]; bounds_dev[n_servers-1]: first
+ * key of servers 1..; *overflow_dev: 1 = a table is full, 2 = an owner segment exceeds land_cap. */
+int64_t psb_sgd_localize_temp_bytes(int64_t max_nnz);
+/* PSB_LOC_TIMING=1 (diagnosis; synchronises after every stage): mean ms per call of {sort, run-length,
+ * sketch, select, columns, owner boundaries, table slots}; returns the calls averaged (0: off). */
+int64_t psb_sgd_localize_timing(double* out7);
+int psb_sgd_localize(const uint64_t* keys, int64_t nnz, uint64_t* sorted, uint64_t* uniq, uint32_t* cnt,
+                     uint8_t* flag, uint64_t* cols, uint32_t* col, int64_t* counts_dev,
+                     uint8_t* sketch, int32_t cm_n, int32_t cm_k, int32_t freq,
+                     const uint64_t* bounds_dev, int32_t n_servers, int64_t land_cap, int64_t* owner_begin,
+                     uint64_t* const* table_keys_host, const int64_t* cap_host, int32_t* col_owner,
+                     int64_t* col_slot, int32_t* overflow_dev, void* temp, int64_t temp_bytes, void* stream);
 int psb_kv_export_nonzero(const uint64_t* keys, const float* w, int64_t cap, uint64_t* out_keys,
                           float* out_w, uint64_t* count_dev, void* stream);
 /* K6+K7+C3+C4: pull, margins / loss / gradient, push of one minibatch in one cooperative launch.
@@ -313,6 +332,67 @@ int psb_sgd_server_update(const psb_sgd_server* sv, uint64_t seq, int32_t grid, 
 int psb_sgd_server_update_fused(const psb_sgd_server* sv, uint64_t seq, int32_t grid, uint32_t* bar,
                                 void* stream);
 
+
+/* Streaming runner (sgd_stream.cu): the whole minibatch loop of a worker + its server in native
+ * code.  Per minibatch, on the runner's copy stream: H2D of the host arrays into one set of a ring of
+ * device buffers, psb_sgd_localize; on the step stream: worker step, server update.  Events order a
+ * set's reuse after the step that read it; the host never waits.  All device memory belongs to the
+ * caller (who keeps it alive until psb_sgd_runner_destroy). */
+#define PSB_SGD_MAX_RING 8
+typedef struct psb_sgd_host_minibatch {  /* pinned host memory; row_ptr starts at 0 */
+  const int64_t* row_ptr;
+  const uint64_t* keys;
+  const float* vals;   /* NULL: binary */
+  const float* y;
+  int64_t n_rows, nnz; /* 0, 0: this rank ran out of data and pushes nothing */
+} psb_sgd_host_minibatch;
+typedef struct psb_sgd_ring_set {
+  int64_t* row_ptr;    /* [max_rows+1] */
+  uint64_t* keys;      /* [max_nnz] */
+  float* vals;         /* [max_nnz] or NULL */
+  float* y;            /* [max_rows] */
+  uint64_t* cols;      /* [max_nnz] localisation outputs ... */
+  uint32_t* col;
+  int32_t* col_owner;
+  int64_t* col_slot;
+  int64_t* counts;     /* [2] */
+  int64_t* owner_begin;/* [n_servers+1] */
+} psb_sgd_ring_set;
+typedef struct psb_sgd_runner_config {
+  psb_sgd_worker worker;  /* peer views, w_local / g_local [max_nnz], xw [max_rows], stats, loss, quant */
+  psb_sgd_server server;
+  psb_sgd_ring_set set[PSB_SGD_MAX_RING];
+  int32_t n_sets;
+  int32_t fused_server;
+  int64_t max_rows, max_nnz;
+  uint64_t* sorted;    /* [max_nnz] scratch of the localisation ... */
+  uint64_t* uniq;
+  uint32_t* cnt;
+  uint8_t* flag;
+  void* temp;
+  int64_t temp_bytes;
+  uint8_t* sketch;     /* tail filter (NULL: none) */
+  int32_t cm_n, cm_k, freq, reserved;
+  const uint64_t* bounds_dev;
+  uint64_t* table_keys[PSB_MAX_PEERS];
+  int64_t table_cap[PSB_MAX_PEERS];
+  int32_t* overflow_dev;
+  int32_t* overflow_host;  /* pinned: receives *overflow_dev at the end of every submit */
+  uint32_t* worker_bar;
+  uint32_t* server_bar;
+  int32_t grid_worker, grid_server;
+  void* copy_stream;
+} psb_sgd_runner_config;
+/* returns NULL on failure (psb_last_error) */
+void* psb_sgd_runner_create(const psb_sgd_runner_config* cfg);
+void psb_sgd_runner_destroy(void* runner);
+/* enqueue n minibatch steps with sequence numbers seq_first, seq_first + 1, ...; returns once
+ * everything is enqueued.  The host arrays must stay valid until the copy stream has passed. */
+/* PSB_SGD_TIMING=1 in the environment at creation: mean ms per step of {H2D, localise, worker kernel,
+ * server kernel, copy stage, step stage, step period}; returns the steps averaged (0: off). */
+int psb_sgd_runner_timing(void* runner, double* out7);
+int psb_sgd_runner_submit(void* runner, const psb_sgd_host_minibatch* mb, int32_t n, uint64_t seq_first,
+                          void* step_stream);
 
 /* ------------------------------------------------------------------------- *
  *  Evaluation, sketches, codecs, fills (eval.cu)

@@ -13,9 +13,11 @@ Two ways to feed it:
                             a minibatch is cached for the following passes up to `cache_bytes`
                             (the device successor of the KEY_CACHING filter);
   train_stream(source)      minibatches arrive from the host (the StreamReader of the reference,
-                            src/learner/sgd.h:104-157): a prefetch thread copies them from pinned
-                            memory (one async copy per array) and localises them on a side stream
-                            while the step kernels of earlier minibatches run; nothing is kept.
+                            src/learner/sgd.h:104-157): the native runner (csrc/cuda/sgd_stream.cu)
+                            copies them from pinned memory into a ring of device buffers and
+                            localises them on a copy stream while the step kernels of earlier
+                            minibatches run; the interpreter only hands over windows of
+                            minibatch descriptors, and nothing is kept.
 The tail-feature filter is the reference's: one CountMin sketch per worker that lives across
 minibatches (insert the counts of a minibatch, keep the keys whose estimate exceeds the bound).
 """
@@ -24,9 +26,7 @@ from __future__ import annotations
 import ctypes as C
 import math
 import os
-import queue
 import sys
-import threading
 import time
 from dataclasses import dataclass
 
@@ -54,7 +54,7 @@ class SgdWorkerStruct(C.Structure):
                 ("land_q", P * MAX_PEERS), ("land_scale", P * MAX_PEERS), ("land_cnt", P * MAX_PEERS),
                 ("land_flag", P * MAX_PEERS), ("ack", P), ("land_cap", C.c_int64),
                 ("rank", C.c_int32), ("n_workers", C.c_int32), ("n_servers", C.c_int32),
-                ("depth", C.c_int32), ("loss", C.c_int32), ("quant", C.c_int32)]
+                ("depth", C.c_int32), ("loss", C.c_int32), ("quant", C.c_int32), ("n_cols_dev", P)]
 
 
 class SgdServerStruct(C.Structure):
@@ -64,6 +64,28 @@ class SgdServerStruct(C.Structure):
                 ("rank", C.c_int32), ("n_workers", C.c_int32), ("depth", C.c_int32),
                 ("algo", C.c_int32), ("quant", C.c_int32), ("alpha", C.c_float), ("beta", C.c_float),
                 ("l1", C.c_float), ("l2", C.c_float), ("sgd_t", C.c_float), ("lr_constant", C.c_int32)]
+
+
+MAX_RING = 8
+
+
+class HostMinibatchStruct(C.Structure):
+    _fields_ = [("row_ptr", P), ("keys", P), ("vals", P), ("y", P), ("n_rows", C.c_int64), ("nnz", C.c_int64)]
+
+
+class RingSetStruct(C.Structure):
+    _fields_ = [("row_ptr", P), ("keys", P), ("vals", P), ("y", P), ("cols", P), ("col", P), ("col_owner", P),
+                ("col_slot", P), ("counts", P), ("owner_begin", P)]
+
+
+class RunnerConfigStruct(C.Structure):
+    _fields_ = [("worker", SgdWorkerStruct), ("server", SgdServerStruct), ("set", RingSetStruct * MAX_RING),
+                ("n_sets", C.c_int32), ("fused_server", C.c_int32), ("max_rows", C.c_int64), ("max_nnz", C.c_int64),
+                ("sorted", P), ("uniq", P), ("cnt", P), ("flag", P), ("temp", P), ("temp_bytes", C.c_int64),
+                ("sketch", P), ("cm_n", C.c_int32), ("cm_k", C.c_int32), ("freq", C.c_int32), ("reserved", C.c_int32),
+                ("bounds_dev", P), ("table_keys", P * MAX_PEERS), ("table_cap", C.c_int64 * MAX_PEERS),
+                ("overflow_dev", P), ("overflow_host", P), ("worker_bar", P), ("server_bar", P),
+                ("grid_worker", C.c_int32), ("grid_server", C.c_int32), ("copy_stream", P)]
 
 
 @dataclass
@@ -85,7 +107,8 @@ class AsyncSGDConfig:
     fixing_float_by_nbytes: int = 0  # != 0 -> block-scaled 8-bit push (K9), see push_format
     push_format: str = "int8"        # int8 | fp8 (e4m3), one fp32 scale per 128 values
     cache_bytes: int = 8 << 30       # resident mode: budget for cached localised minibatches
-    prefetch: int = 3                # streaming mode: localised minibatches kept ahead of the step
+    prefetch: int = 3                # streaming mode: localised minibatches kept ahead of the step (ring = +1)
+    stream_window: int = 64          # streaming mode: minibatches handed to the native runner per call
     table_capacity: int = 1 << 22    # slots per shard (power of two)
     report_every: int = 10           # minibatches between progress lines
     fused_server: bool = True        # one cooperative server launch per step instead of 1 + n_workers
@@ -126,7 +149,12 @@ class _Minibatch:
     col_slot: torch.Tensor
     owner_begin: torch.Tensor
     n_rows: int
-    n_cols: int
+    n_cols: int                       # capacity of the column arrays (the non-zeros of the minibatch)
+    n_cols_dev: torch.Tensor | None = None   # [1] int64 on the device: the actual number of columns
+
+    def kept_keys(self) -> torch.Tensor:
+        """The minibatch's columns (sorted unique keys that passed the tail filter); synchronises."""
+        return self.keys[:int(self.n_cols_dev.item())] if self.n_cols_dev is not None else self.keys[:self.n_cols]
 
 
 def _lib():
@@ -141,6 +169,16 @@ def _lib():
         lib.psb_sgd_server_update_fused.argtypes = [P, C.c_uint64, C.c_int32, P, P]
         lib.psb_sgd_max_grid.restype = C.c_int
         lib.psb_sgd_set_fault_sink.argtypes = [P]
+        lib.psb_sgd_localize_temp_bytes.argtypes = [C.c_int64]
+        lib.psb_sgd_localize_temp_bytes.restype = C.c_int64
+        lib.psb_sgd_runner_create.argtypes = [P]
+        lib.psb_sgd_runner_create.restype = P
+        lib.psb_sgd_runner_destroy.argtypes = [P]
+        lib.psb_sgd_runner_destroy.restype = None
+        lib.psb_sgd_runner_timing.argtypes = [P, P]
+        lib.psb_sgd_runner_submit.argtypes = [P, P, C.c_int32, C.c_uint64, P]
+        lib.psb_sgd_localize.argtypes = [P, C.c_int64, P, P, P, P, P, P, P, P, C.c_int32, C.c_int32, C.c_int32,
+                                         P, C.c_int32, C.c_int64, P, P, P, P, P, P, P, C.c_int64, P]
         lib._sgd_sigs = True
     return lib
 
@@ -158,14 +196,23 @@ class AsyncSGDEngine:
         self.history = []   # (examples, loss, accuracy, auc)
         self._cache = {}
         self._cache_used = 0
-        self.launches = 0
+        self._scratches = {}
+        self._wk = self._w_local = self._g_local = self._xw = None
+        self._step_launches = 0   # written by the step loop
+        self._loc_launches = 0    # written by whichever thread localises
         self.h2d_bytes = 0
-        self.prefetch_busy_s = 0.0   # streaming: wall time the prefetch thread spent localising
-        self.feed_wait_s = 0.0       # streaming: wall time the step loop waited for the prefetcher
+        self.submit_s = 0.0          # streaming: wall time inside the native runner (enqueueing)
+        self.source_s = 0.0          # streaming: wall time spent pulling minibatches from the source
+        self._runner = None
         self.data = None
         self.n_rows = 0
         # PSB_SGD_PROFILE=1: wall time per localisation stage (synchronising after each: slower)
         self._stage_prof = {} if os.environ.get("PSB_SGD_PROFILE") else None
+
+    @property
+    def launches(self) -> int:
+        """Kernels of this framework launched so far (step kernels + localisation kernels)."""
+        return self._step_launches + self._loc_launches
 
     # --------------------------------------------------------------------------------------------
     def load(self, data: SparseCSR, max_unique_per_minibatch: int | None = None) -> None:
@@ -270,82 +317,94 @@ class AsyncSGDEngine:
         return m
 
     def _localize(self, row_ptr: torch.Tensor, keys_nnz: torch.Tensor, vals, y: torch.Tensor) -> _Minibatch:
-        """K10 + K13 + K11 + K15 + K8a on the current stream: unique keys and counts, tail filter,
-        remap to local columns, owner segments, slots in the owners' tables."""
-        cfg, dev = self.cfg, self.device
-        prof = self._stage_prof
-
-        def lap(name, _t=[time.perf_counter()]):
-            if prof is None:
-                return
-            torch.cuda.current_stream(dev).synchronize()
-            now = time.perf_counter()
-            prof[name] = prof.get(name, 0.0) + now - _t[0]
-            _t[0] = now
-        lap("h2d_wait")
+        """K10 + K13 + K11 + K15 + K8a as ONE enqueue on the current stream (psb_sgd_localize):
+        unique keys and counts, tail filter, local column of every non-zero, owner segments, slots
+        in the owners' tables.  No size that depends on the data comes back to the host: the
+        number of columns stays in `n_cols_dev`, and the step kernel reads it there.  The arrays of
+        the returned minibatch have the capacity of its non-zeros."""
+        cfg, dev, W = self.cfg, self.device, self.world
+        t0 = time.perf_counter() if self._stage_prof is not None else 0.0
         nnz, n_rows = keys_nnz.numel(), row_ptr.numel() - 1
-        uniq, cnt = L.unique_count(keys_nnz) if nnz else (keys_nnz, None)
-        lap("sort_unique")
-        if self.tail_sketch is not None and nnz:
-            self.tail_sketch.insert(uniq, cnt.clamp(max=255))
-            uniq = uniq[self.tail_sketch.query_gt(uniq, cfg.tail_feature_freq)].contiguous()
-        n_cols = uniq.numel()
-        lap("tail_filter")
-        idx1 = L.lookup_sorted(uniq, keys_nnz) if nnz else torch.empty(0, dtype=torch.int32, device=dev)
-        rp, col, val = L.compact_csr(row_ptr, idx1, vals)
-        lap("remap")
-        # owners: the sorted unique keys split at the shard boundaries
-        W = self.world
-        if W > 1 and n_cols:
-            cut = L.lower_bound(uniq, self.bounds).tolist()
-        else:
-            cut = [n_cols] * (W - 1)
-        ob = [0] + cut + [n_cols]
-        owner_begin = torch.tensor(ob, dtype=torch.int64, device=dev)
-        col_owner = torch.repeat_interleave(torch.arange(W, dtype=torch.int32, device=dev),
-                                            owner_begin[1:] - owner_begin[:-1]) if n_cols else \
-            torch.zeros(1, dtype=torch.int32, device=dev)
-        col_slot = torch.full((max(n_cols, 1),), -1, dtype=torch.int64, device=dev)
-        lap("owners")
-        if n_cols:
-            assert max(ob[s + 1] - ob[s] for s in range(W)) <= self.land_cap, \
-                "landing region too small: raise max_unique_per_minibatch"
-            check(self.lib.psb_kv_lookup_insert(ptr(uniq), n_cols, ptr(col_owner), self.tab_keys_ptrs,
-                                                self.tab_caps, W, ptr(col_slot), ptr(self.overflow),
-                                                current_stream()))
-        lap("table_slots")
+        cap = max(nnz, 1)
+        i64 = dict(dtype=torch.int64, device=dev)
+        cols = torch.empty(cap, **i64)
+        col_slot = torch.empty(cap, **i64)
+        col = torch.empty(cap, dtype=torch.int32, device=dev)
+        col_owner = torch.empty(cap, dtype=torch.int32, device=dev)
+        counts = torch.empty(2, **i64)
+        owner_begin = torch.empty(W + 1, **i64)
+        sc = self._scratch(cap)
+        sk = self.tail_sketch
+        check(self.lib.psb_sgd_localize(
+            ptr(keys_nnz), nnz, ptr(sc["sorted"]), ptr(sc["uniq"]), ptr(sc["cnt"]), ptr(sc["flag"]),
+            ptr(cols), ptr(col), ptr(counts),
+            sk.table.data_ptr() if sk is not None else None, sk.n if sk is not None else 0,
+            sk.k if sk is not None else 0, cfg.tail_feature_freq,
+            ptr(self.bounds), W, self.land_cap, ptr(owner_begin), self.tab_keys_ptrs, self.tab_caps,
+            ptr(col_owner), ptr(col_slot), ptr(self.overflow), ptr(sc["temp"]), sc["temp"].numel(),
+            current_stream()))
+        self._loc_launches += 5 if sk is not None else 4   # own kernels; the sort / run-length / select are CUB's
         self._new_minibatches = getattr(self, "_new_minibatches", 0) + 1
         if self._new_minibatches % 64 == 0:
             self.check_table_load()
-        lap("load_check")
-        return _Minibatch(rp, col, val, y, uniq, col_owner, col_slot, owner_begin, n_rows, n_cols)
+        if self._stage_prof is not None:
+            torch.cuda.current_stream(dev).synchronize()
+            self._stage_prof["localize"] = self._stage_prof.get("localize", 0.0) + time.perf_counter() - t0
+        return _Minibatch(row_ptr, col, vals, y, cols, col_owner, col_slot, owner_begin, n_rows, nnz, counts[1:])
+
+    def _scratch(self, nnz: int) -> dict:
+        """Work arrays of the localisation, one set per stream that localises (the prefetch stream in
+        streaming mode, the step stream in resident mode): calls on one stream are ordered, so the set
+        is reused from minibatch to minibatch."""
+        key = torch.cuda.current_stream(self.device).cuda_stream
+        sc = self._scratches.get(key)
+        if sc is None or sc["cap"] < nnz:
+            cap = max(nnz, 2 * sc["cap"] if sc else 0)
+            dev = self.device
+            sc = dict(cap=cap,
+                      sorted=torch.empty(cap, dtype=torch.int64, device=dev),
+                      uniq=torch.empty(cap, dtype=torch.int64, device=dev),
+                      cnt=torch.empty(cap, dtype=torch.int32, device=dev),
+                      flag=torch.empty(cap, dtype=torch.uint8, device=dev),
+                      temp=torch.empty(int(self.lib.psb_sgd_localize_temp_bytes(cap)), dtype=torch.uint8, device=dev))
+            self._scratches[key] = sc
+        return sc
 
     def _worker_struct(self, m: _Minibatch):
-        cfg, A, W, D = self.cfg, self.arena, self.world, self.depth
-        dev = self.device
-        nblk = self.land_cap // 128 + 1
-        self._w_local = torch.empty(max(m.n_cols, 1), dtype=torch.float32, device=dev)
-        self._g_local = torch.empty(max(m.n_cols, 1), dtype=torch.float32, device=dev)
-        self._xw = torch.empty(max(m.n_rows, 1), dtype=torch.float32, device=dev)
-        wk = SgdWorkerStruct()
+        """The launch argument of a step: the peer views are filled in once, the fields of the
+        minibatch on every call.  The pulled weights, the gradient and the margins live in buffers
+        that are reused from step to step (all steps run on one stream)."""
+        wk = self._wk
+        if wk is None:
+            cfg, A, W, D, r = self.cfg, self.arena, self.world, self.depth, self.rank
+            nblk = self.land_cap // 128 + 1
+            wk = SgdWorkerStruct()
+            wk.stats = self.wstats.data_ptr()
+            for s in range(W):
+                wk.tab_w[s] = A.peer_ptr(s, self.b_w)
+                wk.land_slot[s] = A.peer_ptr(s, self.b_lslot, r * D * self.land_cap)
+                wk.land_val[s] = A.peer_ptr(s, self.b_lval, r * D * self.land_cap)
+                wk.land_q[s] = A.peer_ptr(s, self.b_lq, r * D * self.land_cap)
+                wk.land_scale[s] = A.peer_ptr(s, self.b_lscale, r * D * nblk)
+                wk.land_cnt[s] = A.peer_ptr(s, self.b_lcnt, r * D)
+                wk.land_flag[s] = A.peer_ptr(s, self.b_lflag, r)
+            wk.ack = self.b_ack.ptr
+            wk.land_cap = self.land_cap
+            wk.rank, wk.n_workers, wk.n_servers, wk.depth = r, W, W, D
+            wk.loss, wk.quant = LOSS[cfg.loss], self.quant
+            self._wk = wk
+        if self._w_local is None or self._w_local.numel() < m.n_cols or self._xw.numel() < m.n_rows:
+            dev = self.device
+            nc = max(m.n_cols, 2 * (self._w_local.numel() if self._w_local is not None else 0), 1)
+            nr = max(m.n_rows, self._xw.numel() if self._xw is not None else 0, 1)
+            self._w_local = torch.empty(nc, dtype=torch.float32, device=dev)
+            self._g_local = torch.empty(nc, dtype=torch.float32, device=dev)
+            self._xw = torch.empty(nr, dtype=torch.float32, device=dev)
+            wk.w_local, wk.g_local, wk.xw = ptr(self._w_local), ptr(self._g_local), ptr(self._xw)
         wk.row_ptr, wk.col, wk.val, wk.y = ptr(m.row_ptr), ptr(m.col), ptr(m.val), ptr(m.y)
         wk.n_rows, wk.n_cols = m.n_rows, m.n_cols
         wk.col_owner, wk.col_slot, wk.owner_begin = ptr(m.col_owner), ptr(m.col_slot), ptr(m.owner_begin)
-        wk.w_local, wk.g_local, wk.xw = ptr(self._w_local), ptr(self._g_local), ptr(self._xw)
-        wk.stats = self.wstats.data_ptr()
-        r = self.rank
-        for s in range(W):
-            wk.tab_w[s] = A.peer_ptr(s, self.b_w)
-            wk.land_slot[s] = A.peer_ptr(s, self.b_lslot, r * D * self.land_cap)
-            wk.land_val[s] = A.peer_ptr(s, self.b_lval, r * D * self.land_cap)
-            wk.land_q[s] = A.peer_ptr(s, self.b_lq, r * D * self.land_cap)
-            wk.land_scale[s] = A.peer_ptr(s, self.b_lscale, r * D * nblk)
-            wk.land_cnt[s] = A.peer_ptr(s, self.b_lcnt, r * D)
-            wk.land_flag[s] = A.peer_ptr(s, self.b_lflag, r)
-        wk.ack = self.b_ack.ptr
-        wk.land_cap = self.land_cap
-        wk.rank, wk.n_workers, wk.n_servers, wk.depth = r, W, W, D
-        wk.loss, wk.quant = LOSS[cfg.loss], self.quant
+        wk.n_cols_dev = ptr(m.n_cols_dev)
         return wk
 
     def worker_step(self, mb):
@@ -357,7 +416,7 @@ class AsyncSGDEngine:
         grid = max(1, min(self.grid, (max(m.n_rows, m.n_cols // 8) + 7) // 8))
         check(self.lib.psb_sgd_worker_step(C.byref(wk), self.seq, grid, self.bar.data_ptr(),
                                            current_stream()))
-        self.launches += 1
+        self._step_launches += 1
         return m
 
     def server_step(self) -> None:
@@ -366,17 +425,21 @@ class AsyncSGDEngine:
         if self.cfg.fused_server:
             check(self.lib.psb_sgd_server_update_fused(C.byref(self.sv), self.seq, self.grid_server,
                                                        self.srv_bar.data_ptr(), current_stream()))
-            self.launches += 1
+            self._step_launches += 1
         else:
             check(self.lib.psb_sgd_server_update(C.byref(self.sv), self.seq, self.grid_server,
                                                  current_stream()))
-            self.launches += 1 + self.world
+            self._step_launches += 1 + self.world
 
     def check_table_load(self) -> float:
         """Open addressing with linear probing degrades sharply when a shard's table fills up
         (probe chains of thousands, each probe a peer round trip for remote workers): refuse to
         crawl.  Returns the load factor of this rank's shard."""
-        if int(self.overflow.item()):
+        code = int(self.overflow.item())
+        if code == 2:
+            raise RuntimeError(f"rank {self.rank}: a minibatch sends more than {self.land_cap} distinct keys to one "
+                               "owner (the landing region): raise max_unique_per_minibatch")
+        if code:
             raise RuntimeError(f"rank {self.rank}: a shard's key table is full (table_capacity="
                                f"{self.cfg.table_capacity}); raise AsyncSGDConfig.table_capacity")
         used = int((self.b_keys.tensor != -1).sum().item())
@@ -423,36 +486,70 @@ class AsyncSGDEngine:
 
     def train_stream(self, source, steps: int, verbose: bool = False, on_step=None) -> int:
         """Streaming mode.  `source` yields host minibatches (SparseCSR whose tensors are in
-        pinned memory); a prefetch thread uploads and localises them `cfg.prefetch` ahead on its
-        own stream.  Runs exactly `steps` steps (the same number on every rank; a rank whose
-        source ends early pushes empty minibatches).  Returns the examples consumed."""
-        feeder = _Prefetcher(self, source, self.cfg.prefetch)
-        feeder.start()
-        main = torch.cuda.current_stream(self.device)
-        seen = 0
+        pinned memory).  Runs exactly `steps` steps (the same number on every rank; a rank whose
+        source ends early pushes empty minibatches) and returns the examples consumed.  Windows of
+        `cfg.stream_window` minibatches are handed to the native runner, which enqueues copy,
+        localisation and both step kernels of every minibatch and returns without waiting for the
+        device.  `on_step(i, m)` is called after the LAST step i of every window (`m`: that
+        minibatch's device arrays, valid until the next window is submitted)."""
+        it = iter(source)
+        main = current_stream()
+        window = max(1, min(self.cfg.stream_window, self.cfg.report_every))
+        seen = done = 0
         t0 = time.time()
-        try:
-            for i in range(steps):
-                t_q = time.perf_counter()
-                item = feeder.get()
-                self.feed_wait_s += time.perf_counter() - t_q
-                if item is None:
-                    m = self.empty_minibatch()
+        ended = False
+        while done < steps:
+            t_a = time.perf_counter()
+            hosts = []
+            while not ended and len(hosts) < min(window, steps - done):
+                h = next(it, None)
+                if h is None:
+                    ended = True
                 else:
-                    m, ready = item
-                    main.wait_event(ready)
-                    for t in (m.row_ptr, m.col, m.val, m.y, m.keys, m.col_owner, m.col_slot, m.owner_begin):
-                        if t is not None:
-                            t.record_stream(main)  # allocated on the prefetch stream, read here
-                self.step(m)
-                seen += m.n_rows
-                if on_step is not None:
-                    on_step(i, m)
-                if verbose and ((i + 1) % self.cfg.report_every == 0 or i + 1 == steps):
-                    self._report(seen, time.time() - t0, m, verbose)
-        finally:
-            feeder.stop()
+                    hosts.append(h)
+            n = min(window, steps - done)
+            t_b = time.perf_counter()
+            self.source_s += t_b - t_a
+            runner = self._stream_runner(max([h.n_rows for h in hosts] + [1]), max([h.nnz for h in hosts] + [1]),
+                                         any(h.vals is not None for h in hosts))
+            last = runner.submit(hosts, n, self.seq + 1, main)
+            self.seq += n
+            self._step_launches += n * (2 if self.cfg.fused_server else 2 + self.world)
+            self._loc_launches += sum((5 if self.tail_sketch is not None else 4) for h in hosts if h.nnz)
+            self.h2d_bytes += sum(8 * (h.n_rows + 1) + 4 * h.n_rows + h.nnz * (8 + (4 if h.vals is not None else 0))
+                                  for h in hosts)
+            self.submit_s += time.perf_counter() - t_b
+            done += n
+            seen += sum(h.n_rows for h in hosts)
+            self._xw = runner.xw
+            self.check_fault()
+            self._check_overflow(runner.overflow_host)
+            if on_step is not None:
+                on_step(done - 1, last)
+            if verbose and (done % self.cfg.report_every == 0 or done == steps):
+                self._report(seen, time.time() - t0, last, verbose)
+        # the load factor of the shard (a scan of the table): once per call, not per window
+        self.check_table_load()
         return seen
+
+    def _stream_runner(self, max_rows: int, max_nnz: int, with_vals: bool):
+        r = self._runner
+        if r is None or r.max_rows < max_rows or r.max_nnz < max_nnz or (with_vals and not r.with_vals):
+            if r is not None:   # a larger minibatch than any before: drain, rebuild the ring
+                max_rows, max_nnz = max(max_rows, r.max_rows), max(max_nnz, 2 * r.max_nnz)
+                with_vals |= r.with_vals
+                r.close()
+            self._runner = r = _StreamRunner(self, max_rows, max_nnz, with_vals)
+        return r
+
+    def _check_overflow(self, flag_host) -> None:
+        code = int(flag_host[0])
+        if code == 2:
+            raise RuntimeError(f"rank {self.rank}: a minibatch sends more than {self.land_cap} distinct keys to one "
+                               "owner (the landing region): raise max_unique_per_minibatch")
+        if code:
+            raise RuntimeError(f"rank {self.rank}: a shard's key table is full (table_capacity="
+                               f"{self.cfg.table_capacity}); raise AsyncSGDConfig.table_capacity")
 
     def _report(self, seen, secs, m, verbose):
         st = self.wstats.cpu().tolist()
@@ -494,77 +591,102 @@ class AsyncSGDEngine:
                                 k.cpu().numpy().view(np.uint64), w.double().cpu().numpy())
 
     def close(self):
+        if self._runner is not None:
+            self._runner.close()
+            self._runner = None
         if hasattr(self, "arena"):
             torch.cuda.synchronize(self.device)
             self.arena.close()
 
 
-class _Prefetcher(threading.Thread):
-    """Host minibatch -> HBM -> localised, ahead of the step loop (the producer half of the
-    reference's MinibatchReader, src/learner/sgd.h:120-129, with the H2D copy in place of the text
-    parser's queue).  One cudaMemcpyAsync per array from pinned memory on a dedicated stream; the
-    host syncs of the localisation (sizes of the unique-key lists) block only this thread."""
+class _StreamRunner:
+    """Owner of the device memory of the native streaming runner (csrc/cuda/sgd_stream.cu): a ring
+    of `prefetch + 1` buffer sets, the scratch of the localisation, the step buffers, the copy
+    stream.  The producer half of the reference's MinibatchReader (src/learner/sgd.h:120-129) with
+    the H2D copy in place of the text parser's queue."""
 
-    def __init__(self, engine, source, depth: int):
-        super().__init__(daemon=True)
-        self.eng, self.source = engine, iter(source)
-        self.q = queue.Queue(maxsize=max(1, depth))
-        self.stream = torch.cuda.Stream(engine.device)
-        self._halt = threading.Event()
-        self._ended = False
-        self.error = None
+    def __init__(self, eng: "AsyncSGDEngine", max_rows: int, max_nnz: int, with_vals: bool):
+        dev, W, lib = eng.device, eng.world, eng.lib
+        self.eng, self.max_rows, self.max_nnz, self.with_vals = eng, max_rows, max_nnz, with_vals
+        self.copy_stream = torch.cuda.Stream(dev)
+        n_sets = max(2, min(MAX_RING, eng.cfg.prefetch + 1))
+        i64, i32, f32 = (dict(dtype=t, device=dev) for t in (torch.int64, torch.int32, torch.float32))
+        self.sets = []
+        cfg = RunnerConfigStruct()
+        eng._w_local = eng._g_local = eng._xw = None
+        probe = _Minibatch(None, None, None, None, None, None, None, None, max_rows, max_nnz, None)
+        wk = eng._worker_struct(probe)        # peer views + step buffers of this capacity
+        self.xw = eng._xw
+        C.memmove(C.byref(cfg.worker), C.byref(wk), C.sizeof(SgdWorkerStruct))
+        C.memmove(C.byref(cfg.server), C.byref(eng.sv), C.sizeof(SgdServerStruct))
+        for i in range(n_sets):
+            t = dict(row_ptr=torch.zeros(max_rows + 1, **i64), keys=torch.empty(max_nnz, **i64),
+                     vals=torch.empty(max_nnz, **f32) if with_vals else None, y=torch.empty(max_rows, **f32),
+                     cols=torch.empty(max_nnz, **i64), col=torch.empty(max_nnz, **i32),
+                     col_owner=torch.empty(max_nnz, **i32), col_slot=torch.empty(max_nnz, **i64),
+                     counts=torch.zeros(2, **i64), owner_begin=torch.zeros(W + 1, **i64))
+            self.sets.append(t)
+            for name, v in t.items():
+                setattr(cfg.set[i], name, ptr(v))
+        self.scratch = dict(sorted=torch.empty(max_nnz, **i64), uniq=torch.empty(max_nnz, **i64),
+                            cnt=torch.empty(max_nnz, **i32), flag=torch.empty(max_nnz, dtype=torch.uint8, device=dev),
+                            temp=torch.empty(int(lib.psb_sgd_localize_temp_bytes(max_nnz)), dtype=torch.uint8, device=dev))
+        for name in ("sorted", "uniq", "cnt", "flag", "temp"):
+            setattr(cfg, name, ptr(self.scratch[name]))
+        cfg.temp_bytes = self.scratch["temp"].numel()
+        cfg.n_sets, cfg.fused_server = n_sets, int(eng.cfg.fused_server)
+        cfg.max_rows, cfg.max_nnz = max_rows, max_nnz
+        sk = eng.tail_sketch
+        if sk is not None:
+            cfg.sketch, cfg.cm_n, cfg.cm_k, cfg.freq = sk.table.data_ptr(), sk.n, sk.k, eng.cfg.tail_feature_freq
+        cfg.bounds_dev = ptr(eng.bounds)
+        for s in range(W):
+            cfg.table_keys[s], cfg.table_cap[s] = eng.tab_keys_ptrs[s], eng.tab_caps[s]
+        self.overflow_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        cfg.overflow_dev, cfg.overflow_host = ptr(eng.overflow), self.overflow_host.data_ptr()
+        cfg.worker_bar, cfg.server_bar = eng.bar.data_ptr(), eng.srv_bar.data_ptr()
+        cfg.grid_worker, cfg.grid_server = eng.grid, eng.grid_server
+        cfg.copy_stream = self.copy_stream.cuda_stream
+        torch.cuda.synchronize(dev)           # the buffers above were filled on the current stream
+        self.handle = lib.psb_sgd_runner_create(C.byref(cfg))
+        if not self.handle:
+            check(1)
+        self.count = 0
+        self._hosts = []                       # host arrays of the windows whose copies may still be in flight
 
-    def run(self):
-        eng, dev = self.eng, self.eng.device
-        try:
-            torch.cuda.set_device(dev)
-            with torch.cuda.stream(self.stream):
-                for host in self.source:
-                    if self._halt.is_set():
-                        return
-                    up = lambda t: None if t is None else t.to(dev, non_blocking=True)  # noqa: E731
-                    rp, keys, vals, y = up(host.row_ptr), up(host.keys), up(host.vals), up(host.y)
-                    eng.h2d_bytes += sum(t.numel() * t.element_size() for t in (rp, keys, vals, y) if t is not None)
-                    t_loc = time.perf_counter()
-                    m = eng._localize(rp, keys, vals, y)
-                    eng.prefetch_busy_s += time.perf_counter() - t_loc
-                    ready = torch.cuda.Event()
-                    ready.record(self.stream)
-                    while not self._halt.is_set():
-                        try:
-                            self.q.put((m, ready), timeout=0.1)
-                            break
-                        except queue.Full:
-                            continue
-        except BaseException as e:  # noqa: BLE001 - surfaced by get()
-            self.error = e
-        finally:
-            while not self._halt.is_set():
-                try:
-                    self.q.put(None, timeout=0.1)
-                    break
-                except queue.Full:
-                    continue
+    def submit(self, hosts: list, n: int, seq_first: int, step_stream) -> _Minibatch:
+        """Enqueue `n` steps: the minibatches of `hosts`, then empty ones.  Returns the device view
+        of the last one."""
+        descs = (HostMinibatchStruct * n)()
+        for d, h in zip(descs, hosts):
+            d.row_ptr, d.keys, d.vals, d.y = h.row_ptr.data_ptr(), h.keys.data_ptr(), ptr(h.vals), h.y.data_ptr()
+            d.n_rows, d.nnz = h.n_rows, h.nnz
+        check(self.eng.lib.psb_sgd_runner_submit(self.handle, descs, n, seq_first, step_stream))
+        done = torch.cuda.Event()
+        done.record(self.copy_stream)
+        self._hosts.append((hosts, done))
+        while len(self._hosts) > 2:            # two windows back: its copies are long done
+            self._hosts.pop(0)[1].synchronize()
+        self.count += n
+        t = self.sets[(self.count - 1) % len(self.sets)]
+        rows = hosts[n - 1].n_rows if len(hosts) == n else 0
+        nnz = hosts[n - 1].nnz if len(hosts) == n else 0
+        return _Minibatch(t["row_ptr"][:rows + 1], t["col"][:nnz], t["vals"][:nnz] if t["vals"] is not None else None,
+                          t["y"][:rows], t["cols"], t["col_owner"], t["col_slot"], t["owner_begin"], rows, nnz,
+                          t["counts"][1:])
 
-    def get(self):
-        """The next localised minibatch, or None once the source is exhausted (and from then on)."""
-        if self._ended:
-            return None
-        item = self.q.get()
-        if self.error is not None:
-            raise self.error
-        if item is None:
-            self._ended = True
-        return item
+    def timing(self) -> dict | None:
+        """PSB_SGD_TIMING=1: mean device milliseconds per step of the stages (synchronises)."""
+        out = (C.c_double * 7)()
+        n = self.eng.lib.psb_sgd_runner_timing(self.handle, out)
+        names = ("h2d", "localize", "worker", "server", "copy_stage", "step_stage", "period")
+        return dict(zip(names, (round(v, 4) for v in out)), steps=n) if n else None
 
-    def stop(self):
-        self._halt.set()
-        while True:
-            try:
-                self.q.get_nowait()
-            except queue.Empty:
-                break
-        self.join(timeout=10)
+    def close(self):
+        if self.handle:
+            torch.cuda.synchronize(self.eng.device)
+            self.eng.lib.psb_sgd_runner_destroy(self.handle)
+            self.handle = None
 
 
 def _as_i64(u: int) -> int:

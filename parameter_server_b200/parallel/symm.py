@@ -11,6 +11,7 @@ where only the offset arithmetic is exercised).
 from __future__ import annotations
 
 import ctypes
+import os
 from dataclasses import dataclass
 
 import torch
@@ -50,7 +51,13 @@ class SymmetricArena:
         self.rank, self.world, self.group = rank, world, group
         self.device = torch.device(device if device is not None else
                                    f"cuda:{torch.cuda.current_device()}")
-        self.nbytes = (int(nbytes) + 4095) // 4096 * 4096
+        # The size MUST be a multiple of the 2 MB device page.  Measured on B200 (benchmarks/micro/
+        # peer_random.cu, benchmarks/peer_table_probe.py; profiles/README.md section 0.5): a cudaMalloc of
+        # 2 GB + 4 KB, exported through cudaIpc, costs a peer 1 320 us for 200 000 random 8-byte reads,
+        # the same allocation rounded to 2 MB 41 us; coalesced bulk transfers do not show the difference.
+        # PSB_ARENA_GRANULE exists only to reproduce that measurement.
+        granule = int(os.environ.get("PSB_ARENA_GRANULE", 2 << 20))
+        self.nbytes = (int(nbytes) + granule - 1) // granule * granule
         base = ctypes.c_void_p(0)
         with torch.cuda.device(self.device):
             check(self.lib.psb_malloc(ctypes.byref(base), self.nbytes))

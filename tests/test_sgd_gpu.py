@@ -229,7 +229,7 @@ def test_sgd_tail_filter_is_the_persistent_host_sketch():
         seen_k.append(uniq); seen_c.append(np.minimum(cnt, 255).astype(np.uint8))
         keep, _ = host.countmin_filter(np.concatenate(seen_k), np.concatenate(seen_c), n=eng.tail_sketch.n, k=2, freq=2)
         want = uniq[keep[-uniq.size:]]
-        assert np.array_equal(m.keys.cpu().numpy().view(np.uint64), want), mb
+        assert np.array_equal(m.kept_keys().cpu().numpy().view(np.uint64), want), mb
         # a key that shows up once per minibatch is dropped at first and kept later
         kept_any_late |= mb >= 2 and bool(np.any(cnt[keep[-uniq.size:]] == 1))
     assert kept_any_late
@@ -265,3 +265,38 @@ def test_sgd_streaming_equals_resident():
     assert st.h2d_bytes > 0 and torch.equal(k0, k1) and torch.allclose(w0, w1, rtol=1e-6, atol=1e-7)
     assert st.wstats.cpu().tolist()[0] == pytest.approx(loss0, rel=1e-6)
     st.close()
+
+
+def test_sgd_localize_matches_numpy():
+    """psb_sgd_localize (one enqueue, all sizes on the device) against a numpy restatement: kept
+    keys, local column of every non-zero, owner segments, and slots that hold the right keys."""
+    from parameter_server_b200.models.async_sgd import AsyncSGDConfig, AsyncSGDEngine
+    from parameter_server_b200.utils.synthetic import make_rcv1_like
+    dev = torch.device("cuda:0")
+    data = make_rcv1_like(600, 5000, 12.0, seed=21, device=dev)
+    for freq in (0, 1):
+        cfg = AsyncSGDConfig(minibatch=300, tail_feature_freq=freq, countmin_n=1 << 24, table_capacity=1 << 14)
+        eng = AsyncSGDEngine(cfg, None, dev)
+        eng.load(data)
+        for mb in range(2):
+            m = eng._prepare(mb)
+            lo, hi = int(data.row_ptr[mb * 300]), int(data.row_ptr[(mb + 1) * 300])
+            keys = data.keys[lo:hi].cpu().numpy().view(np.uint64)
+            kept = m.kept_keys().cpu().numpy().view(np.uint64)
+            uniq, cnt = np.unique(keys, return_counts=True)
+            if freq == 0:
+                assert np.array_equal(kept, uniq)
+            else:  # first minibatch: exactly the keys seen more than once (no collisions at this size)
+                assert np.all(np.diff(kept.astype(np.int64)) > 0) and set(kept) <= set(uniq)
+                if mb == 0:
+                    assert np.array_equal(kept, uniq[cnt > freq])
+            col = m.col[:hi - lo].cpu().numpy().view(np.uint32)
+            pos = np.searchsorted(kept, keys)
+            hit = (pos < kept.size) & (kept[np.minimum(pos, kept.size - 1)] == keys)
+            assert np.array_equal(col[hit], pos[hit].astype(np.uint32)) and np.all(col[~hit] == 0xffffffff)
+            assert m.owner_begin.tolist() == [0, kept.size]
+            slots = m.col_slot[:kept.size].cpu().numpy()
+            table = eng.b_keys.tensor.cpu().numpy().view(np.uint64)
+            assert np.all(slots >= 0) and np.array_equal(table[slots], kept)
+            assert np.all(m.col_owner[:kept.size].cpu().numpy() == 0)
+        eng.close()
