@@ -1,3 +1,4 @@
+# Reproduces profiles/README.md section 0.5 on a box with 2 GPUs (results under gpurun_out/).
 run() { tag=$1; shift; env "$@" timeout 100 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29513 benchmarks/peer_table_probe.py > gpurun_out/probe_$tag.log 2>&1; echo "== $tag rc=$?"; grep -E '"peer, (one|all)' gpurun_out/probe_$tag.log; }
 run granule_4k PSB_ARENA_GRANULE=4096
 run granule_2m PSB_ARENA_GRANULE=2097152

@@ -29,8 +29,14 @@ namespace PS {
 
 class PeerVan : public Van {
  public:
+  // an exported allocation that is not a whole number of 2 MB device pages makes random peer access
+  // ~30x slower on B200 (benchmarks/micro/peer_random.cu)
+  static size_t roundToDevicePage(size_t bytes) {
+    const size_t page = size_t(2) << 20;
+    return std::max(page, (bytes + page - 1) / page * page);
+  }
   PeerVan(unique_ptr<Van> inner, int gpu, size_t arena_bytes, const string& dir)
-      : inner_(std::move(inner)), gpu_(gpu), arena_bytes_(arena_bytes / 4096 * 4096), dir_(dir) {}
+      : inner_(std::move(inner)), gpu_(gpu), arena_bytes_(roundToDevicePage(arena_bytes)), dir_(dir) {}
   ~PeerVan() override { shutdown(); release(); }
 
   bool init(NodeView my_node) override {
