@@ -183,25 +183,16 @@ PSB_API int64_t psb_sgd_localize_temp_bytes(int64_t max_nnz) {
   return (int64_t)m + 256;
 }
 
-// One enqueue, no host synchronisation.  Device buffers of capacity nnz: sorted, uniq, cnt, flag,
-// cols (out: kept keys), col (out: local column per non-zero, 0xffffffff = filtered), col_owner,
-// col_slot (out); counts[2] (out, device): {unique keys, kept keys = columns}; owner_begin[W+1] (out).
-// sketch == NULL: no tail filter.  bounds_dev[W-1]: first key of servers 1..W-1.
-// table_keys_host[s] / cap_host[s]: this process' mapping of server s' key table.
-// *overflow_dev: 1 = a table is full, 2 = an owner segment exceeds land_cap.
-PSB_API int psb_sgd_localize(const uint64_t* keys, int64_t nnz, uint64_t* sorted, uint64_t* uniq, uint32_t* cnt,
-                             uint8_t* flag, uint64_t* cols, uint32_t* col, int64_t* counts_dev,
-                             uint8_t* sketch, int32_t cm_n, int32_t cm_k, int32_t freq,
-                             const uint64_t* bounds_dev, int32_t n_servers, int64_t land_cap, int64_t* owner_begin,
-                             uint64_t* const* table_keys_host, const int64_t* cap_host, int32_t* col_owner,
-                             int64_t* col_slot, int32_t* overflow_dev, void* temp, int64_t temp_bytes,
-                             void* stream) {
-  PSB_REQUIRE(n_servers >= 1 && n_servers <= PSB_MAX_PEERS, "psb_sgd_localize: n_servers=%d", n_servers);
+// The localisation in two stages, so that a caller may overlap stage A of one minibatch with stage B of
+// the one before (stage B touches the sketch, whose updates must stay in minibatch order).
+//
+// Stage A: keys[nnz] -> sorted[nnz] -> uniq / cnt (capacity nnz), counts_dev[0] = number of unique keys.
+PSB_API int psb_sgd_localize_sort(const uint64_t* keys, int64_t nnz, uint64_t* sorted, uint64_t* uniq, uint32_t* cnt,
+                                  int64_t* counts_dev, void* temp, int64_t temp_bytes, void* stream) {
   PSB_REQUIRE(nnz >= 0 && nnz < (1LL << 31), "psb_sgd_localize: nnz=%lld", (long long)nnz);
   cudaStream_t st = (cudaStream_t)stream;
   if (nnz == 0) {
     PSB_CUDA(cudaMemsetAsync(counts_dev, 0, 2 * sizeof(int64_t), st));
-    PSB_CUDA(cudaMemsetAsync(owner_begin, 0, (n_servers + 1) * sizeof(int64_t), st));
     return 0;
   }
   double t_lap = 0;
@@ -212,13 +203,35 @@ PSB_API int psb_sgd_localize(const uint64_t* keys, int64_t nnz, uint64_t* sorted
   bytes = (size_t)temp_bytes;
   PSB_CUDA(cub::DeviceRunLengthEncode::Encode(temp, bytes, sorted, uniq, cnt, counts_dev, (int)nnz, st));
   LOC_LAP(1)
+  return 0;
+}
+
+// Stage B: tail filter (sketch == NULL: none) -> cols (kept keys), counts_dev[1] = their number -> col (local
+// column per non-zero, 0xffffffff = filtered) -> owner_begin[W+1], col_owner -> col_slot.
+// bounds_dev[W-1]: first key of servers 1..W-1.  table_keys_host[s] / cap_host[s]: this process' mapping
+// of server s' key table.  *overflow_dev: 1 = a table is full, 2 = an owner segment exceeds land_cap.
+PSB_API int psb_sgd_localize_finish(const uint64_t* keys, int64_t nnz, const uint64_t* uniq, const uint32_t* cnt,
+                                    uint8_t* flag, uint64_t* cols, uint32_t* col, int64_t* counts_dev,
+                                    uint8_t* sketch, int32_t cm_n, int32_t cm_k, int32_t freq,
+                                    const uint64_t* bounds_dev, int32_t n_servers, int64_t land_cap,
+                                    int64_t* owner_begin, uint64_t* const* table_keys_host, const int64_t* cap_host,
+                                    int32_t* col_owner, int64_t* col_slot, int32_t* overflow_dev, void* temp,
+                                    int64_t temp_bytes, void* stream) {
+  PSB_REQUIRE(n_servers >= 1 && n_servers <= PSB_MAX_PEERS, "psb_sgd_localize: n_servers=%d", n_servers);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (nnz == 0) {
+    PSB_CUDA(cudaMemsetAsync(owner_begin, 0, (n_servers + 1) * sizeof(int64_t), st));
+    return 0;
+  }
+  double t_lap = 0;
+  if (g_loc_timing.on) { cudaStreamSynchronize(st); t_lap = now_s(); }
   if (sketch) {
     PSB_REQUIRE(cm_n >= 64 && cm_n % 4 == 0 && cm_k >= 1 && cm_k <= 30, "psb_sgd_localize: bad sketch size");
     k_loc_sketch_insert<<<grid_of(nnz), 256, 0, st>>>(uniq, cnt, counts_dev, sketch, (uint32_t)cm_n, cm_k);
   }
   k_loc_sketch_query<<<grid_of(nnz), 256, 0, st>>>(uniq, counts_dev, nnz, sketch, (uint32_t)cm_n, cm_k, freq, flag);
   LOC_LAP(2)
-  bytes = (size_t)temp_bytes;
+  size_t bytes = (size_t)temp_bytes;
   PSB_CUDA(cub::DeviceSelect::Flagged(temp, bytes, uniq, flag, cols, counts_dev + 1, (int)nnz, st));
   LOC_LAP(3)
   k_loc_columns<<<grid_of(nnz), 256, 0, st>>>(cols, counts_dev + 1, keys, nnz, col);
@@ -236,6 +249,22 @@ PSB_API int psb_sgd_localize(const uint64_t* keys, int64_t nnz, uint64_t* sorted
   PSB_LAUNCH_CHECK();
   LOC_LAP(6)
   return 0;
+}
+
+// Both stages as one enqueue, no host synchronisation.  Device buffers of capacity nnz: sorted, uniq, cnt,
+// flag, cols, col, col_owner, col_slot; counts_dev[2] <- {unique keys, kept keys = columns}.
+PSB_API int psb_sgd_localize(const uint64_t* keys, int64_t nnz, uint64_t* sorted, uint64_t* uniq, uint32_t* cnt,
+                             uint8_t* flag, uint64_t* cols, uint32_t* col, int64_t* counts_dev,
+                             uint8_t* sketch, int32_t cm_n, int32_t cm_k, int32_t freq,
+                             const uint64_t* bounds_dev, int32_t n_servers, int64_t land_cap, int64_t* owner_begin,
+                             uint64_t* const* table_keys_host, const int64_t* cap_host, int32_t* col_owner,
+                             int64_t* col_slot, int32_t* overflow_dev, void* temp, int64_t temp_bytes,
+                             void* stream) {
+  int rc = psb_sgd_localize_sort(keys, nnz, sorted, uniq, cnt, counts_dev, temp, temp_bytes, stream);
+  if (rc) return rc;
+  return psb_sgd_localize_finish(keys, nnz, uniq, cnt, flag, cols, col, counts_dev, sketch, cm_n, cm_k, freq,
+                                 bounds_dev, n_servers, land_cap, owner_begin, table_keys_host, cap_host, col_owner,
+                                 col_slot, overflow_dev, temp, temp_bytes, stream);
 }
 
 // PSB_LOC_TIMING=1: mean milliseconds per call of {sort, run-length, sketch insert + query, select,

@@ -4,9 +4,13 @@
 // processMinibatch, src/app/linear_method/async_sgd.h:217-290); here the loop body is a fixed
 // sequence of enqueues, so the runner issues it without the interpreter in between:
 //
-//   copy stream:  [wait: the step that last read this ring set]  H2D row_ptr / keys / vals / y
-//                 -> psb_sgd_localize (sort, tail filter, columns, owners, slots)  -> event `ready`
+//   copy stream k & 1:  [wait: the step that last read this ring set]  H2D row_ptr / keys / vals / y
+//                 -> stage A (sort, run-length)  -> [wait `ready` of minibatch k - 1: the sketch is updated
+//                 in minibatch order]  -> stage B (tail filter, columns, owners, slots)  -> event `ready`
 //   step stream:  [wait `ready`]  worker step (pull, gradient, push)  ->  server update  -> event `done`
+//
+// Two copy streams with their own scratch let stage A of a minibatch overlap stage B of the one before:
+// both are chains of small latency-bound kernels.
 //
 // Nothing on the host waits for the device; sizes that depend on the data never leave it.
 #include <cmath>
@@ -24,6 +28,7 @@ struct SgdRunner {
   cudaEvent_t done[PSB_SGD_MAX_RING];
   bool used[PSB_SGD_MAX_RING];
   uint64_t next = 0;  // minibatches submitted so far (ring position)
+  int prev_slot = -1; // ring set of the minibatch submitted last
   int n_events = 0;
   // PSB_SGD_TIMING=1: device time stamps of the stages of the first kTimedSteps steps
   // (copy stream: start, after H2D, after localise; step stream: start, after worker, after server)
@@ -52,7 +57,8 @@ PSB_API void psb_sgd_runner_destroy(void* runner) {
 
 PSB_API void* psb_sgd_runner_create(const psb_sgd_runner_config* cfg) {
   if (!cfg || cfg->n_sets < 1 || cfg->n_sets > PSB_SGD_MAX_RING || cfg->max_rows < 1 || cfg->max_nnz < 1 ||
-      !cfg->worker_bar || !cfg->overflow_dev || !cfg->temp) {
+      !cfg->worker_bar || !cfg->overflow_dev || !cfg->scratch[0].temp || !cfg->scratch[1].temp ||
+      cfg->n_sets < 2) {
     set_error("psb_sgd_runner_create: bad configuration");
     return nullptr;
   }
@@ -108,7 +114,8 @@ PSB_API int psb_sgd_runner_submit(void* runner, const psb_sgd_host_minibatch* mb
   SgdRunner* r = static_cast<SgdRunner*>(runner);
   PSB_REQUIRE(r && (mb || n == 0) && n >= 0 && seq_first >= 1, "psb_sgd_runner_submit: bad argument");
   const psb_sgd_runner_config& c = r->c;
-  cudaStream_t copy = (cudaStream_t)c.copy_stream, step = (cudaStream_t)step_stream;
+  cudaStream_t step = (cudaStream_t)step_stream;
+  cudaStream_t copy = nullptr;
   const int W = c.worker.n_servers;
   for (int i = 0; i < n; ++i) {
     const psb_sgd_host_minibatch& h = mb[i];
@@ -118,6 +125,9 @@ PSB_API int psb_sgd_runner_submit(void* runner, const psb_sgd_host_minibatch* mb
     const int slot = (int)(r->next % (uint64_t)c.n_sets);
     const psb_sgd_ring_set& s = c.set[slot];
     const uint64_t seq = seq_first + (uint64_t)i;
+    const int lane = (int)(r->next & 1);
+    copy = (cudaStream_t)c.copy_stream[lane];
+    const psb_sgd_scratch& sc = c.scratch[lane];
 
     // ---- copy stream: upload and localise ----
     if (r->used[slot]) PSB_CUDA(cudaStreamWaitEvent(copy, r->done[slot], 0));
@@ -135,10 +145,12 @@ PSB_API int psb_sgd_runner_submit(void* runner, const psb_sgd_host_minibatch* mb
       }
     }
     if (stamp) cudaEventRecord(stamp[1], copy);
-    int rc = psb_sgd_localize(s.keys, h.nnz, c.sorted, c.uniq, c.cnt, c.flag, s.cols, s.col, s.counts, c.sketch,
-                              c.cm_n, c.cm_k, c.freq, c.bounds_dev, W, c.worker.land_cap, s.owner_begin,
-                              c.table_keys, c.table_cap, s.col_owner, s.col_slot, c.overflow_dev, c.temp,
-                              c.temp_bytes, copy);
+    int rc = psb_sgd_localize_sort(s.keys, h.nnz, sc.sorted, sc.uniq, sc.cnt, s.counts, sc.temp, c.temp_bytes, copy);
+    if (rc) return rc;
+    if (r->prev_slot >= 0) PSB_CUDA(cudaStreamWaitEvent(copy, r->ready[r->prev_slot], 0));
+    rc = psb_sgd_localize_finish(s.keys, h.nnz, sc.uniq, sc.cnt, sc.flag, s.cols, s.col, s.counts, c.sketch, c.cm_n,
+                                 c.cm_k, c.freq, c.bounds_dev, W, c.worker.land_cap, s.owner_begin, c.table_keys,
+                                 c.table_cap, s.col_owner, s.col_slot, c.overflow_dev, sc.temp, c.temp_bytes, copy);
     if (rc) return rc;
     if (stamp) cudaEventRecord(stamp[2], copy);
     PSB_CUDA(cudaEventRecord(r->ready[slot], copy));
@@ -164,9 +176,10 @@ PSB_API int psb_sgd_runner_submit(void* runner, const psb_sgd_host_minibatch* mb
     if (stamp) cudaEventRecord(stamp[5], step);
     PSB_CUDA(cudaEventRecord(r->done[slot], step));
     r->used[slot] = true;
+    r->prev_slot = slot;
     ++r->next;
   }
-  if (c.overflow_host)
+  if (c.overflow_host && copy)  // `copy` ran stage B of the last minibatch, which waited for all earlier ones
     PSB_CUDA(cudaMemcpyAsync(c.overflow_host, c.overflow_dev, sizeof(int32_t), cudaMemcpyDeviceToHost, copy));
   return 0;
 }

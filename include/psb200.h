@@ -308,6 +308,16 @@ int64_t psb_sgd_localize_temp_bytes(int64_t max_nnz);
 /* PSB_LOC_TIMING=1 (diagnosis; synchronises after every stage): mean ms per call of {sort, run-length,
  * sketch, select, columns, owner boundaries, table slots}; returns the calls averaged (0: off). */
 int64_t psb_sgd_localize_timing(double* out7);
+/* the two stages on their own (stage B touches the sketch and must run in minibatch order; stage A of
+ * the next minibatch may overlap it on another stream, with its own sorted / uniq / cnt / temp) */
+int psb_sgd_localize_sort(const uint64_t* keys, int64_t nnz, uint64_t* sorted, uint64_t* uniq, uint32_t* cnt,
+                          int64_t* counts_dev, void* temp, int64_t temp_bytes, void* stream);
+int psb_sgd_localize_finish(const uint64_t* keys, int64_t nnz, const uint64_t* uniq, const uint32_t* cnt,
+                            uint8_t* flag, uint64_t* cols, uint32_t* col, int64_t* counts_dev,
+                            uint8_t* sketch, int32_t cm_n, int32_t cm_k, int32_t freq,
+                            const uint64_t* bounds_dev, int32_t n_servers, int64_t land_cap, int64_t* owner_begin,
+                            uint64_t* const* table_keys_host, const int64_t* cap_host, int32_t* col_owner,
+                            int64_t* col_slot, int32_t* overflow_dev, void* temp, int64_t temp_bytes, void* stream);
 int psb_sgd_localize(const uint64_t* keys, int64_t nnz, uint64_t* sorted, uint64_t* uniq, uint32_t* cnt,
                      uint8_t* flag, uint64_t* cols, uint32_t* col, int64_t* counts_dev,
                      uint8_t* sketch, int32_t cm_n, int32_t cm_k, int32_t freq,
@@ -334,9 +344,10 @@ int psb_sgd_server_update_fused(const psb_sgd_server* sv, uint64_t seq, int32_t 
 
 
 /* Streaming runner (sgd_stream.cu): the whole minibatch loop of a worker + its server in native
- * code.  Per minibatch, on the runner's copy stream: H2D of the host arrays into one set of a ring of
- * device buffers, psb_sgd_localize; on the step stream: worker step, server update.  Events order a
- * set's reuse after the step that read it; the host never waits.  All device memory belongs to the
+ * code.  Per minibatch, on one of the runner's two copy streams (alternating): H2D of the host arrays into
+ * one set of a ring of device buffers, stage A of the localisation, then - after stage B of the previous
+ * minibatch on the other stream - stage B; on the step stream: worker step, server update.  Events
+ * order a set's reuse after the step that read it; the host never waits.  All device memory belongs to the
  * caller (who keeps it alive until psb_sgd_runner_destroy). */
 #define PSB_SGD_MAX_RING 8
 typedef struct psb_sgd_host_minibatch {  /* pinned host memory; row_ptr starts at 0 */
@@ -358,6 +369,13 @@ typedef struct psb_sgd_ring_set {
   int64_t* counts;     /* [2] */
   int64_t* owner_begin;/* [n_servers+1] */
 } psb_sgd_ring_set;
+typedef struct psb_sgd_scratch {  /* work arrays of one localisation in flight */
+  uint64_t* sorted;    /* [max_nnz] */
+  uint64_t* uniq;      /* [max_nnz] */
+  uint32_t* cnt;       /* [max_nnz] */
+  uint8_t* flag;       /* [max_nnz] */
+  void* temp;          /* [temp_bytes] psb_sgd_localize_temp_bytes(max_nnz) */
+} psb_sgd_scratch;
 typedef struct psb_sgd_runner_config {
   psb_sgd_worker worker;  /* peer views, w_local / g_local [max_nnz], xw [max_rows], stats, loss, quant */
   psb_sgd_server server;
@@ -365,11 +383,7 @@ typedef struct psb_sgd_runner_config {
   int32_t n_sets;
   int32_t fused_server;
   int64_t max_rows, max_nnz;
-  uint64_t* sorted;    /* [max_nnz] scratch of the localisation ... */
-  uint64_t* uniq;
-  uint32_t* cnt;
-  uint8_t* flag;
-  void* temp;
+  psb_sgd_scratch scratch[2];  /* minibatch k localises with scratch[k & 1] on copy_stream[k & 1] */
   int64_t temp_bytes;
   uint8_t* sketch;     /* tail filter (NULL: none) */
   int32_t cm_n, cm_k, freq, reserved;
@@ -381,7 +395,7 @@ typedef struct psb_sgd_runner_config {
   uint32_t* worker_bar;
   uint32_t* server_bar;
   int32_t grid_worker, grid_server;
-  void* copy_stream;
+  void* copy_stream[2];  /* two, so that the sort of one minibatch overlaps the rest of the one before */
 } psb_sgd_runner_config;
 /* returns NULL on failure (psb_last_error) */
 void* psb_sgd_runner_create(const psb_sgd_runner_config* cfg);

@@ -78,14 +78,18 @@ class RingSetStruct(C.Structure):
                 ("col_slot", P), ("counts", P), ("owner_begin", P)]
 
 
+class ScratchStruct(C.Structure):
+    _fields_ = [("sorted", P), ("uniq", P), ("cnt", P), ("flag", P), ("temp", P)]
+
+
 class RunnerConfigStruct(C.Structure):
     _fields_ = [("worker", SgdWorkerStruct), ("server", SgdServerStruct), ("set", RingSetStruct * MAX_RING),
                 ("n_sets", C.c_int32), ("fused_server", C.c_int32), ("max_rows", C.c_int64), ("max_nnz", C.c_int64),
-                ("sorted", P), ("uniq", P), ("cnt", P), ("flag", P), ("temp", P), ("temp_bytes", C.c_int64),
+                ("scratch", ScratchStruct * 2), ("temp_bytes", C.c_int64),
                 ("sketch", P), ("cm_n", C.c_int32), ("cm_k", C.c_int32), ("freq", C.c_int32), ("reserved", C.c_int32),
                 ("bounds_dev", P), ("table_keys", P * MAX_PEERS), ("table_cap", C.c_int64 * MAX_PEERS),
                 ("overflow_dev", P), ("overflow_host", P), ("worker_bar", P), ("server_bar", P),
-                ("grid_worker", C.c_int32), ("grid_server", C.c_int32), ("copy_stream", P)]
+                ("grid_worker", C.c_int32), ("grid_server", C.c_int32), ("copy_stream", P * 2)]
 
 
 @dataclass
@@ -601,14 +605,14 @@ class AsyncSGDEngine:
 
 class _StreamRunner:
     """Owner of the device memory of the native streaming runner (csrc/cuda/sgd_stream.cu): a ring
-    of `prefetch + 1` buffer sets, the scratch of the localisation, the step buffers, the copy
-    stream.  The producer half of the reference's MinibatchReader (src/learner/sgd.h:120-129) with
+    of `prefetch + 1` buffer sets, two scratch sets of the localisation, the step buffers, the two
+    copy streams.  The producer half of the reference's MinibatchReader (src/learner/sgd.h:120-129) with
     the H2D copy in place of the text parser's queue."""
 
     def __init__(self, eng: "AsyncSGDEngine", max_rows: int, max_nnz: int, with_vals: bool):
         dev, W, lib = eng.device, eng.world, eng.lib
         self.eng, self.max_rows, self.max_nnz, self.with_vals = eng, max_rows, max_nnz, with_vals
-        self.copy_stream = torch.cuda.Stream(dev)
+        self.copy_streams = [torch.cuda.Stream(dev), torch.cuda.Stream(dev)]
         n_sets = max(2, min(MAX_RING, eng.cfg.prefetch + 1))
         i64, i32, f32 = (dict(dtype=t, device=dev) for t in (torch.int64, torch.int32, torch.float32))
         self.sets = []
@@ -628,12 +632,14 @@ class _StreamRunner:
             self.sets.append(t)
             for name, v in t.items():
                 setattr(cfg.set[i], name, ptr(v))
-        self.scratch = dict(sorted=torch.empty(max_nnz, **i64), uniq=torch.empty(max_nnz, **i64),
-                            cnt=torch.empty(max_nnz, **i32), flag=torch.empty(max_nnz, dtype=torch.uint8, device=dev),
-                            temp=torch.empty(int(lib.psb_sgd_localize_temp_bytes(max_nnz)), dtype=torch.uint8, device=dev))
-        for name in ("sorted", "uniq", "cnt", "flag", "temp"):
-            setattr(cfg, name, ptr(self.scratch[name]))
-        cfg.temp_bytes = self.scratch["temp"].numel()
+        temp_bytes = int(lib.psb_sgd_localize_temp_bytes(max_nnz))
+        self.scratch = [dict(sorted=torch.empty(max_nnz, **i64), uniq=torch.empty(max_nnz, **i64),
+                             cnt=torch.empty(max_nnz, **i32), flag=torch.empty(max_nnz, dtype=torch.uint8, device=dev),
+                             temp=torch.empty(temp_bytes, dtype=torch.uint8, device=dev)) for _ in range(2)]
+        for lane, sc in enumerate(self.scratch):
+            for name, v in sc.items():
+                setattr(cfg.scratch[lane], name, ptr(v))
+        cfg.temp_bytes = temp_bytes
         cfg.n_sets, cfg.fused_server = n_sets, int(eng.cfg.fused_server)
         cfg.max_rows, cfg.max_nnz = max_rows, max_nnz
         sk = eng.tail_sketch
@@ -646,7 +652,8 @@ class _StreamRunner:
         cfg.overflow_dev, cfg.overflow_host = ptr(eng.overflow), self.overflow_host.data_ptr()
         cfg.worker_bar, cfg.server_bar = eng.bar.data_ptr(), eng.srv_bar.data_ptr()
         cfg.grid_worker, cfg.grid_server = eng.grid, eng.grid_server
-        cfg.copy_stream = self.copy_stream.cuda_stream
+        for lane, st in enumerate(self.copy_streams):
+            cfg.copy_stream[lane] = st.cuda_stream
         torch.cuda.synchronize(dev)           # the buffers above were filled on the current stream
         self.handle = lib.psb_sgd_runner_create(C.byref(cfg))
         if not self.handle:
@@ -662,11 +669,13 @@ class _StreamRunner:
             d.row_ptr, d.keys, d.vals, d.y = h.row_ptr.data_ptr(), h.keys.data_ptr(), ptr(h.vals), h.y.data_ptr()
             d.n_rows, d.nnz = h.n_rows, h.nnz
         check(self.eng.lib.psb_sgd_runner_submit(self.handle, descs, n, seq_first, step_stream))
-        done = torch.cuda.Event()
-        done.record(self.copy_stream)
-        self._hosts.append((hosts, done))
+        copied = [torch.cuda.Event() for _ in self.copy_streams]
+        for ev, st in zip(copied, self.copy_streams):
+            ev.record(st)
+        self._hosts.append((hosts, copied))
         while len(self._hosts) > 2:            # two windows back: its copies are long done
-            self._hosts.pop(0)[1].synchronize()
+            for ev in self._hosts.pop(0)[1]:
+                ev.synchronize()
         self.count += n
         t = self.sets[(self.count - 1) % len(self.sets)]
         rows = hosts[n - 1].n_rows if len(hosts) == n else 0

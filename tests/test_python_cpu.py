@@ -1,6 +1,8 @@
 """CPU-only checks of the Python layer: config mapping, model files, front-end helpers, generators."""
 import os
 
+import pytest
+
 import numpy as np
 import torch
 
@@ -90,3 +92,25 @@ def test_multi_rank_protocol_model():
     assert pc.check(ranks=2, keys=9, blocks=3, passes=5, schedules=60, seed=7, verbose=False) == 0
     assert pc.check(schedules=60, mutate="no_flow", verbose=False) > 0      # writers ignore the done flags
     assert pc.check(schedules=60, mutate="no_parity", verbose=False) > 0    # one buffer instead of two per step parity
+
+
+def test_sgd_ctypes_mirrors_have_the_c_sizes(tmp_path):
+    """The ctypes structures of models/async_sgd.py are hand-written mirrors of include/psb200.h: a
+    field added on one side only shifts every later field silently.  Compare sizeof on both sides."""
+    import ctypes as C
+    import shutil
+    import subprocess
+    from parameter_server_b200.models import async_sgd as m
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "sz.cpp"
+    src.write_text('#include <cstdio>\n#include "%s/include/psb200.h"\nint main() { printf("%%zu %%zu %%zu %%zu %%zu\\n", '
+                   'sizeof(psb_sgd_worker), sizeof(psb_sgd_server), sizeof(psb_sgd_runner_config), '
+                   'sizeof(psb_sgd_host_minibatch), sizeof(psb_sgd_ring_set)); }\n' % root)
+    exe = tmp_path / "sz"
+    subprocess.run(["g++", "-std=c++17", str(src), "-o", str(exe)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
+    want = [C.sizeof(t) for t in (m.SgdWorkerStruct, m.SgdServerStruct, m.RunnerConfigStruct,
+                                  m.HostMinibatchStruct, m.RingSetStruct)]
+    assert got == want
