@@ -201,6 +201,11 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl"])
+    ap.add_argument("--config", default="darlin", choices=["darlin", "ctr_sgd"],
+                    help="darlin: the headline (BASELINE configs 1 / 2); ctr_sgd: BASELINE configs 3 / 4, streaming "
+                         "async SGD at the named CTR size - delegates to benchmarks/ctr_sgd_stream.py, whose own "
+                         "options (--examples-per-gpu, --passes, --push ...) may follow; it is timed from the first "
+                         "minibatch of the first pass, so --steps / --warmup do not apply")
     ap.add_argument("--rows", type=int, default=677399, help="examples per GPU")
     ap.add_argument("--features", type=int, default=47236)
     ap.add_argument("--nnz-per-row", type=float, default=73.2)
@@ -215,7 +220,14 @@ def main() -> None:
     ap.add_argument("--split", action="store_true", help="3 kernels per step instead of the persistent pass kernel")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling sub-benchmark (N > 1)")
     ap.add_argument("--no-tto", action="store_true", help="skip the time-to-objective phase")
-    args = ap.parse_args()
+    args, rest = ap.parse_known_args()
+    if args.config == "ctr_sgd" and args.impl == "ours":
+        sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "benchmarks"))
+        import ctr_sgd_stream
+        ctr_sgd_stream.main(rest)
+        return
+    if rest:
+        ap.error("unrecognized arguments: " + " ".join(rest))
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) == 0:
             reference_arm(args)

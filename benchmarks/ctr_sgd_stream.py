@@ -101,7 +101,7 @@ class HostData:
                                  self.y[a:a + rows], 1 << 63)
 
 
-def main():
+def main(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--examples-per-gpu", type=int, default=12_500_000)
     ap.add_argument("--passes", type=int, default=10)
@@ -113,7 +113,7 @@ def main():
     ap.add_argument("--tail-freq", type=int, default=1)
     ap.add_argument("--push", default="fp32", choices=["fp32", "int8", "fp8"])
     ap.add_argument("--table-capacity", type=int, default=0, help="slots per shard (0: from the data size)")
-    args = ap.parse_args()
+    args = ap.parse_args(argv)
     from parameter_server_b200.models.async_sgd import AsyncSGDConfig, AsyncSGDEngine
     from parameter_server_b200.ops.evaluation import auc as dev_auc
     from parameter_server_b200.parallel.comm import SingleComm, TorchComm
