@@ -160,7 +160,7 @@ def main(argv=None):
 
     def keep_last(i, m):
         if i == steps - 1 and m.n_rows:
-            last["y"], last["xw"] = m.y, eng._xw[:m.n_rows].clone()
+            last["y"], last["xw"] = m.y.clone(), m.xw[:m.n_rows].clone()
 
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.passes + 1)]
     l0 = eng.launches

@@ -155,6 +155,7 @@ class _Minibatch:
     n_rows: int
     n_cols: int                       # capacity of the column arrays (the non-zeros of the minibatch)
     n_cols_dev: torch.Tensor | None = None   # [1] int64 on the device: the actual number of columns
+    xw: torch.Tensor | None = None           # streaming: the buffer that holds this step's margins afterwards
 
     def kept_keys(self) -> torch.Tensor:
         """The minibatch's columns (sorted unique keys that passed the tail filter); synchronises."""
@@ -374,10 +375,11 @@ class AsyncSGDEngine:
             self._scratches[key] = sc
         return sc
 
-    def _worker_struct(self, m: _Minibatch):
-        """The launch argument of a step: the peer views are filled in once, the fields of the
-        minibatch on every call.  The pulled weights, the gradient and the margins live in buffers
-        that are reused from step to step (all steps run on one stream)."""
+    def _worker_template(self, max_cols: int, max_rows: int):
+        """The part of the step's launch argument that does not depend on the minibatch: the peer
+        views (filled in once) and the buffers of the pulled weights, the gradient and the margins,
+        grown to at least (max_cols, max_rows) and reused from step to step - all steps run on one
+        stream."""
         wk = self._wk
         if wk is None:
             cfg, A, W, D, r = self.cfg, self.arena, self.world, self.depth, self.rank
@@ -397,14 +399,20 @@ class AsyncSGDEngine:
             wk.rank, wk.n_workers, wk.n_servers, wk.depth = r, W, W, D
             wk.loss, wk.quant = LOSS[cfg.loss], self.quant
             self._wk = wk
-        if self._w_local is None or self._w_local.numel() < m.n_cols or self._xw.numel() < m.n_rows:
+        have_c = self._w_local.numel() if self._w_local is not None else 0
+        have_r = self._xw.numel() if self._xw is not None else 0
+        if have_c < max_cols or have_r < max_rows:
             dev = self.device
-            nc = max(m.n_cols, 2 * (self._w_local.numel() if self._w_local is not None else 0), 1)
-            nr = max(m.n_rows, self._xw.numel() if self._xw is not None else 0, 1)
+            nc, nr = max(max_cols, 2 * have_c, 1), max(max_rows, have_r, 1)
             self._w_local = torch.empty(nc, dtype=torch.float32, device=dev)
             self._g_local = torch.empty(nc, dtype=torch.float32, device=dev)
             self._xw = torch.empty(nr, dtype=torch.float32, device=dev)
             wk.w_local, wk.g_local, wk.xw = ptr(self._w_local), ptr(self._g_local), ptr(self._xw)
+        return wk
+
+    def _worker_struct(self, m: _Minibatch):
+        """The launch argument of the step on minibatch `m`."""
+        wk = self._worker_template(m.n_cols, m.n_rows)
         wk.row_ptr, wk.col, wk.val, wk.y = ptr(m.row_ptr), ptr(m.col), ptr(m.val), ptr(m.y)
         wk.n_rows, wk.n_cols = m.n_rows, m.n_cols
         wk.col_owner, wk.col_slot, wk.owner_begin = ptr(m.col_owner), ptr(m.col_slot), ptr(m.owner_begin)
@@ -525,7 +533,6 @@ class AsyncSGDEngine:
             self.submit_s += time.perf_counter() - t_b
             done += n
             seen += sum(h.n_rows for h in hosts)
-            self._xw = runner.xw
             self.check_fault()
             self._check_overflow(runner.overflow_host)
             if on_step is not None:
@@ -562,7 +569,7 @@ class AsyncSGDEngine:
         auc = float("nan")
         if m.n_rows:
             from ..ops.evaluation import auc as dev_auc
-            auc = dev_auc(m.y, self._xw[:m.n_rows])
+            auc = dev_auc(m.y, (m.xw if m.xw is not None else self._xw)[:m.n_rows])
         ss = self.sstats.cpu().tolist()
         self.sstats[1:].zero_()
         rec = dict(examples=seen, loss=st[0] / rows, accuracy=st[1] / rows, auc=auc, nnz_w=ss[0],
@@ -617,10 +624,9 @@ class _StreamRunner:
         i64, i32, f32 = (dict(dtype=t, device=dev) for t in (torch.int64, torch.int32, torch.float32))
         self.sets = []
         cfg = RunnerConfigStruct()
-        eng._w_local = eng._g_local = eng._xw = None
-        probe = _Minibatch(None, None, None, None, None, None, None, None, max_rows, max_nnz, None)
-        wk = eng._worker_struct(probe)        # peer views + step buffers of this capacity
-        self.xw = eng._xw
+        wk = eng._worker_template(max_nnz, max_rows)   # peer views + step buffers of this capacity
+        # the native side keeps these addresses: hold the tensors even if the engine replaces its own
+        self.w_local, self.g_local, self.xw = eng._w_local, eng._g_local, eng._xw
         C.memmove(C.byref(cfg.worker), C.byref(wk), C.sizeof(SgdWorkerStruct))
         C.memmove(C.byref(cfg.server), C.byref(eng.sv), C.sizeof(SgdServerStruct))
         for i in range(n_sets):
@@ -682,7 +688,7 @@ class _StreamRunner:
         nnz = hosts[n - 1].nnz if len(hosts) == n else 0
         return _Minibatch(t["row_ptr"][:rows + 1], t["col"][:nnz], t["vals"][:nnz] if t["vals"] is not None else None,
                           t["y"][:rows], t["cols"], t["col_owner"], t["col_slot"], t["owner_begin"], rows, nnz,
-                          t["counts"][1:])
+                          t["counts"][1:], self.xw)
 
     def timing(self) -> dict | None:
         """PSB_SGD_TIMING=1: mean device milliseconds per step of the stages (synchronises)."""

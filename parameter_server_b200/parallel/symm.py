@@ -44,6 +44,15 @@ class SymmBuffer:
         return self.tensor.data_ptr()
 
 
+DEVICE_PAGE = 2 << 20
+
+
+def arena_bytes(nbytes: int) -> int:
+    """Size of the allocation behind an arena of `nbytes`: whole device pages (see SymmetricArena)."""
+    granule = int(os.environ.get("PSB_ARENA_GRANULE", DEVICE_PAGE))
+    return max(granule, (int(nbytes) + granule - 1) // granule * granule)
+
+
 class SymmetricArena:
     def __init__(self, nbytes: int, rank: int = 0, world: int = 1, group=None, device=None):
         apply_cuda_sigs()
@@ -56,8 +65,7 @@ class SymmetricArena:
         # 2 GB + 4 KB, exported through cudaIpc, costs a peer 1 320 us for 200 000 random 8-byte reads,
         # the same allocation rounded to 2 MB 41 us; coalesced bulk transfers do not show the difference.
         # PSB_ARENA_GRANULE exists only to reproduce that measurement.
-        granule = int(os.environ.get("PSB_ARENA_GRANULE", 2 << 20))
-        self.nbytes = (int(nbytes) + granule - 1) // granule * granule
+        self.nbytes = arena_bytes(nbytes)
         base = ctypes.c_void_p(0)
         with torch.cuda.device(self.device):
             check(self.lib.psb_malloc(ctypes.byref(base), self.nbytes))

@@ -94,6 +94,21 @@ def test_multi_rank_protocol_model():
     assert pc.check(schedules=60, mutate="no_parity", verbose=False) > 0    # one buffer instead of two per step parity
 
 
+def test_streaming_runner_ordering_model():
+    """tools/runner_check.py: random interleavings of the copy lanes and the step stream of the native
+    async-SGD runner (ring sets, two scratch sets, sketch order) hold the invariants with the events
+    the runner records, and the checker notices each missing one."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("runner_check", f"{ROOT}/tools/runner_check.py")
+    rc = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(rc)
+    for ring in (2, 3, 5, 8):
+        assert rc.check(ring=ring, minibatches=30, schedules=60, verbose=False) == 0
+    assert rc.check(schedules=120, mutate="no_done", verbose=False) > 0       # ring set reused without waiting
+    assert rc.check(schedules=40, mutate="no_order", verbose=False) > 0       # stage B not chained
+    assert rc.check(schedules=40, mutate="one_scratch", verbose=False) > 0    # both lanes on one scratch set
+
+
 def test_sgd_ctypes_mirrors_have_the_c_sizes(tmp_path):
     """The ctypes structures of models/async_sgd.py are hand-written mirrors of include/psb200.h: a
     field added on one side only shifts every later field silently.  Compare sizeof on both sides."""
@@ -114,3 +129,13 @@ def test_sgd_ctypes_mirrors_have_the_c_sizes(tmp_path):
     want = [C.sizeof(t) for t in (m.SgdWorkerStruct, m.SgdServerStruct, m.RunnerConfigStruct,
                                   m.HostMinibatchStruct, m.RingSetStruct)]
     assert got == want
+
+
+def test_arena_is_whole_device_pages(monkeypatch):
+    """Exported allocations must be multiples of the 2 MB device page: random peer access to any other
+    size was measured 30x slower (profiles/README.md section 0.5)."""
+    from parameter_server_b200.parallel.symm import DEVICE_PAGE, arena_bytes
+    monkeypatch.delenv("PSB_ARENA_GRANULE", raising=False)
+    for n in (1, 4096, DEVICE_PAGE - 1, DEVICE_PAGE, DEVICE_PAGE + 1, (2 << 30) + 4096, 5_400_000_123):
+        b = arena_bytes(n)
+        assert b >= n and b % DEVICE_PAGE == 0 and b - n < DEVICE_PAGE
