@@ -4,13 +4,13 @@
 // processMinibatch, src/app/linear_method/async_sgd.h:217-290); here the loop body is a fixed
 // sequence of enqueues, so the runner issues it without the interpreter in between:
 //
-//   copy stream k & 1:  [wait: the step that last read this ring set]  H2D row_ptr / keys / vals / y
+//   copy stream k % L:  [wait: the step that last read this ring set]  H2D row_ptr / keys / vals / y
 //                 -> stage A (sort, run-length)  -> [wait `ready` of minibatch k - 1: the sketch is updated
 //                 in minibatch order]  -> stage B (tail filter, columns, owners, slots)  -> event `ready`
 //   step stream:  [wait `ready`]  worker step (pull, gradient, push)  ->  server update  -> event `done`
 //
-// Two copy streams with their own scratch let stage A of a minibatch overlap stage B of the one before:
-// both are chains of small latency-bound kernels.
+// L copy streams ("lanes") with their own scratch let upload and stage A of a minibatch overlap stage B
+// of those before: all of them are chains of small latency-bound operations.
 //
 // Nothing on the host waits for the device; sizes that depend on the data never leave it.
 #include <cmath>
@@ -57,11 +57,16 @@ PSB_API void psb_sgd_runner_destroy(void* runner) {
 
 PSB_API void* psb_sgd_runner_create(const psb_sgd_runner_config* cfg) {
   if (!cfg || cfg->n_sets < 1 || cfg->n_sets > PSB_SGD_MAX_RING || cfg->max_rows < 1 || cfg->max_nnz < 1 ||
-      !cfg->worker_bar || !cfg->overflow_dev || !cfg->scratch[0].temp || !cfg->scratch[1].temp ||
-      cfg->n_sets < 2) {
+      !cfg->worker_bar || !cfg->overflow_dev || cfg->n_lanes < 1 || cfg->n_lanes > PSB_SGD_MAX_LANES ||
+      cfg->n_sets <= cfg->n_lanes) {
     set_error("psb_sgd_runner_create: bad configuration");
     return nullptr;
   }
+  for (int l = 0; l < cfg->n_lanes; ++l)
+    if (!cfg->scratch[l].temp || !cfg->scratch[l].sorted || !cfg->copy_stream[l]) {
+      set_error("psb_sgd_runner_create: lane %d has no scratch or no stream", l);
+      return nullptr;
+    }
   SgdRunner* r = new (std::nothrow) SgdRunner();
   if (!r) return nullptr;
   r->c = *cfg;
@@ -125,7 +130,7 @@ PSB_API int psb_sgd_runner_submit(void* runner, const psb_sgd_host_minibatch* mb
     const int slot = (int)(r->next % (uint64_t)c.n_sets);
     const psb_sgd_ring_set& s = c.set[slot];
     const uint64_t seq = seq_first + (uint64_t)i;
-    const int lane = (int)(r->next & 1);
+    const int lane = (int)(r->next % (uint64_t)c.n_lanes);
     copy = (cudaStream_t)c.copy_stream[lane];
     const psb_sgd_scratch& sc = c.scratch[lane];
 

@@ -344,12 +344,13 @@ int psb_sgd_server_update_fused(const psb_sgd_server* sv, uint64_t seq, int32_t 
 
 
 /* Streaming runner (sgd_stream.cu): the whole minibatch loop of a worker + its server in native
- * code.  Per minibatch, on one of the runner's two copy streams (alternating): H2D of the host arrays into
+ * code.  Per minibatch, on one of the runner's copy streams (round robin): H2D of the host arrays into
  * one set of a ring of device buffers, stage A of the localisation, then - after stage B of the previous
- * minibatch on the other stream - stage B; on the step stream: worker step, server update.  Events
+ * minibatch on another stream - stage B; on the step stream: worker step, server update.  Events
  * order a set's reuse after the step that read it; the host never waits.  All device memory belongs to the
  * caller (who keeps it alive until psb_sgd_runner_destroy). */
-#define PSB_SGD_MAX_RING 8
+#define PSB_SGD_MAX_RING 12
+#define PSB_SGD_MAX_LANES 8
 typedef struct psb_sgd_host_minibatch {  /* pinned host memory; row_ptr starts at 0 */
   const int64_t* row_ptr;
   const uint64_t* keys;
@@ -383,7 +384,7 @@ typedef struct psb_sgd_runner_config {
   int32_t n_sets;
   int32_t fused_server;
   int64_t max_rows, max_nnz;
-  psb_sgd_scratch scratch[2];  /* minibatch k localises with scratch[k & 1] on copy_stream[k & 1] */
+  psb_sgd_scratch scratch[PSB_SGD_MAX_LANES];  /* minibatch k localises with scratch[k % n_lanes] on copy_stream[k % n_lanes] */
   int64_t temp_bytes;
   uint8_t* sketch;     /* tail filter (NULL: none) */
   int32_t cm_n, cm_k, freq, reserved;
@@ -395,7 +396,9 @@ typedef struct psb_sgd_runner_config {
   uint32_t* worker_bar;
   uint32_t* server_bar;
   int32_t grid_worker, grid_server;
-  void* copy_stream[2];  /* two, so that the sort of one minibatch overlaps the rest of the one before */
+  void* copy_stream[PSB_SGD_MAX_LANES];  /* several, so that upload and sort of one minibatch overlap the rest of those before */
+  int32_t n_lanes;       /* 1 .. PSB_SGD_MAX_LANES, and < n_sets */
+  int32_t reserved2;
 } psb_sgd_runner_config;
 /* returns NULL on failure (psb_last_error) */
 void* psb_sgd_runner_create(const psb_sgd_runner_config* cfg);

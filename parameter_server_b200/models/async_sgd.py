@@ -66,7 +66,8 @@ class SgdServerStruct(C.Structure):
                 ("l1", C.c_float), ("l2", C.c_float), ("sgd_t", C.c_float), ("lr_constant", C.c_int32)]
 
 
-MAX_RING = 8
+MAX_RING = 12
+MAX_LANES = 8
 
 
 class HostMinibatchStruct(C.Structure):
@@ -85,11 +86,12 @@ class ScratchStruct(C.Structure):
 class RunnerConfigStruct(C.Structure):
     _fields_ = [("worker", SgdWorkerStruct), ("server", SgdServerStruct), ("set", RingSetStruct * MAX_RING),
                 ("n_sets", C.c_int32), ("fused_server", C.c_int32), ("max_rows", C.c_int64), ("max_nnz", C.c_int64),
-                ("scratch", ScratchStruct * 2), ("temp_bytes", C.c_int64),
+                ("scratch", ScratchStruct * MAX_LANES), ("temp_bytes", C.c_int64),
                 ("sketch", P), ("cm_n", C.c_int32), ("cm_k", C.c_int32), ("freq", C.c_int32), ("reserved", C.c_int32),
                 ("bounds_dev", P), ("table_keys", P * MAX_PEERS), ("table_cap", C.c_int64 * MAX_PEERS),
                 ("overflow_dev", P), ("overflow_host", P), ("worker_bar", P), ("server_bar", P),
-                ("grid_worker", C.c_int32), ("grid_server", C.c_int32), ("copy_stream", P * 2)]
+                ("grid_worker", C.c_int32), ("grid_server", C.c_int32), ("copy_stream", P * MAX_LANES),
+                ("n_lanes", C.c_int32), ("reserved2", C.c_int32)]
 
 
 @dataclass
@@ -113,6 +115,7 @@ class AsyncSGDConfig:
     cache_bytes: int = 8 << 30       # resident mode: budget for cached localised minibatches
     prefetch: int = 3                # streaming mode: localised minibatches kept ahead of the step (ring = +1)
     stream_window: int = 64          # streaming mode: minibatches handed to the native runner per call
+    copy_lanes: int = 4              # streaming mode: minibatches uploaded / localised concurrently (1..8)
     table_capacity: int = 1 << 22    # slots per shard (power of two)
     report_every: int = 10           # minibatches between progress lines
     fused_server: bool = True        # one cooperative server launch per step instead of 1 + n_workers
@@ -612,15 +615,16 @@ class AsyncSGDEngine:
 
 class _StreamRunner:
     """Owner of the device memory of the native streaming runner (csrc/cuda/sgd_stream.cu): a ring
-    of `prefetch + 1` buffer sets, two scratch sets of the localisation, the step buffers, the two
-    copy streams.  The producer half of the reference's MinibatchReader (src/learner/sgd.h:120-129) with
+    of buffer sets, one scratch set of the localisation and one copy stream per lane (`copy_lanes`
+    minibatches are uploaded / localised concurrently), the step buffers.  The producer half of the reference's MinibatchReader (src/learner/sgd.h:120-129) with
     the H2D copy in place of the text parser's queue."""
 
     def __init__(self, eng: "AsyncSGDEngine", max_rows: int, max_nnz: int, with_vals: bool):
         dev, W, lib = eng.device, eng.world, eng.lib
         self.eng, self.max_rows, self.max_nnz, self.with_vals = eng, max_rows, max_nnz, with_vals
-        self.copy_streams = [torch.cuda.Stream(dev), torch.cuda.Stream(dev)]
-        n_sets = max(2, min(MAX_RING, eng.cfg.prefetch + 1))
+        n_lanes = max(1, min(MAX_LANES, int(os.environ.get("PSB_SGD_COPY_LANES", eng.cfg.copy_lanes))))
+        self.copy_streams = [torch.cuda.Stream(dev) for _ in range(n_lanes)]
+        n_sets = min(MAX_RING, max(n_lanes + 1, eng.cfg.prefetch + 1))
         i64, i32, f32 = (dict(dtype=t, device=dev) for t in (torch.int64, torch.int32, torch.float32))
         self.sets = []
         cfg = RunnerConfigStruct()
@@ -641,12 +645,12 @@ class _StreamRunner:
         temp_bytes = int(lib.psb_sgd_localize_temp_bytes(max_nnz))
         self.scratch = [dict(sorted=torch.empty(max_nnz, **i64), uniq=torch.empty(max_nnz, **i64),
                              cnt=torch.empty(max_nnz, **i32), flag=torch.empty(max_nnz, dtype=torch.uint8, device=dev),
-                             temp=torch.empty(temp_bytes, dtype=torch.uint8, device=dev)) for _ in range(2)]
+                             temp=torch.empty(temp_bytes, dtype=torch.uint8, device=dev)) for _ in range(n_lanes)]
         for lane, sc in enumerate(self.scratch):
             for name, v in sc.items():
                 setattr(cfg.scratch[lane], name, ptr(v))
         cfg.temp_bytes = temp_bytes
-        cfg.n_sets, cfg.fused_server = n_sets, int(eng.cfg.fused_server)
+        cfg.n_sets, cfg.n_lanes, cfg.fused_server = n_sets, n_lanes, int(eng.cfg.fused_server)
         cfg.max_rows, cfg.max_nnz = max_rows, max_nnz
         sk = eng.tail_sketch
         if sk is not None:

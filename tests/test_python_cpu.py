@@ -102,11 +102,12 @@ def test_streaming_runner_ordering_model():
     spec = importlib.util.spec_from_file_location("runner_check", f"{ROOT}/tools/runner_check.py")
     rc = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(rc)
-    for ring in (2, 3, 5, 8):
-        assert rc.check(ring=ring, minibatches=30, schedules=60, verbose=False) == 0
-    assert rc.check(schedules=120, mutate="no_done", verbose=False) > 0       # ring set reused without waiting
-    assert rc.check(schedules=40, mutate="no_order", verbose=False) > 0       # stage B not chained
-    assert rc.check(schedules=40, mutate="one_scratch", verbose=False) > 0    # both lanes on one scratch set
+    for ring, lanes in ((2, 1), (3, 2), (4, 3), (5, 3), (5, 4), (8, 4)):
+        assert rc.check(ring=ring, lanes=lanes, minibatches=30, schedules=50, verbose=False) == 0
+    for lanes in (2, 3):
+        assert rc.check(schedules=150, lanes=lanes, mutate="no_done", verbose=False) > 0     # ring set reused without waiting
+        assert rc.check(schedules=40, lanes=lanes, mutate="no_order", verbose=False) > 0     # stage B not chained
+        assert rc.check(schedules=40, lanes=lanes, mutate="one_scratch", verbose=False) > 0  # all lanes on one scratch set
 
 
 def test_sgd_ctypes_mirrors_have_the_c_sizes(tmp_path):

@@ -1,6 +1,6 @@
 """Randomised interleaving check of the streaming runner's ordering (csrc/cuda/sgd_stream.cu):
-minibatch k is uploaded and localised on copy lane k & 1 into ring set k % R with scratch k & 1, and
-stepped on the step stream; the only ordering between the three streams are the events the runner
+minibatch k is uploaded and localised on copy lane k % L into ring set k % R with scratch k % L, and
+stepped on the step stream; the only ordering between the streams are the events the runner
 records and waits for.
 
 It is a model of the enqueue order, not of the CUDA code: every stream is a FIFO of operations, an
@@ -12,7 +12,7 @@ a seeded random scheduler picks among the runnable heads.  Checked on every sche
   * the sketch (stage B) is updated in minibatch order;
   * no deadlock.
 
-    python tools/runner_check.py [--ring 5] [--minibatches 40] [--schedules 300] [--mutate no_done]
+    python tools/runner_check.py [--ring 5] [--lanes 3] [--minibatches 40] [--schedules 300] [--mutate no_done]
 """
 from __future__ import annotations
 
@@ -20,13 +20,14 @@ import argparse
 import random
 
 
-def program(n_mb: int, ring: int, mutate: str):
+def program(n_mb: int, ring: int, mutate: str, lanes: int = 2):
     """The operations the runner enqueues, per stream, in order.  op = (kind, k, waits, records)."""
-    streams = {"copy0": [], "copy1": [], "step": []}
+    streams = {f"copy{l}": [] for l in range(lanes)}
+    streams["step"] = []
     used = [False] * ring
     prev_slot = None
     for k in range(n_mb):
-        slot, lane = k % ring, k & 1
+        slot, lane = k % ring, k % lanes
         if mutate == "one_scratch":
             lane_scratch = 0
         else:
@@ -48,14 +49,14 @@ def program(n_mb: int, ring: int, mutate: str):
 
 
 class Model:
-    def __init__(self, n_mb, ring, rng, mutate=""):
+    def __init__(self, n_mb, ring, rng, mutate="", lanes=2):
         self.rng, self.ring = rng, ring
-        self.streams = program(n_mb, ring, mutate)
+        self.streams = program(n_mb, ring, mutate, lanes)
         self.pos = {s: 0 for s in self.streams}
         self.fired = set()                 # (event kind, slot, minibatch) as recorded
         self.set_holds = [None] * ring     # minibatch whose data the ring set holds (None: being written / empty)
         self.set_state = ["empty"] * ring  # empty | uploaded | sorted | ready | reading
-        self.scratch_holds = [None, None]  # minibatch whose uniq / cnt the scratch set holds
+        self.scratch_holds = [None] * lanes  # minibatch whose uniq / cnt the scratch set holds
         self.sketch_next = 0
         self.errors = []
         # operations are not atomic: model each as begin / end so that overlaps are visible
@@ -124,10 +125,10 @@ class Model:
         return self.errors
 
 
-def check(ring=5, minibatches=40, schedules=300, seed=0, mutate="", verbose=True) -> int:
+def check(ring=5, minibatches=40, schedules=300, seed=0, mutate="", verbose=True, lanes=2) -> int:
     bad = 0
     for i in range(schedules):
-        errs = Model(minibatches, ring, random.Random(seed * 7919 + i), mutate).run()
+        errs = Model(minibatches, ring, random.Random(seed * 7919 + i), mutate, lanes).run()
         if errs:
             bad += 1
             if verbose:
@@ -138,11 +139,12 @@ def check(ring=5, minibatches=40, schedules=300, seed=0, mutate="", verbose=True
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--ring", type=int, default=5)
+    ap.add_argument("--lanes", type=int, default=3)
     ap.add_argument("--minibatches", type=int, default=40)
     ap.add_argument("--schedules", type=int, default=300)
     ap.add_argument("--mutate", default="", choices=["", "no_done", "no_order", "one_scratch"],
                     help="break the ordering on purpose: the checker must notice")
     a = ap.parse_args()
-    n = check(a.ring, a.minibatches, a.schedules, mutate=a.mutate)
+    n = check(a.ring, a.minibatches, a.schedules, mutate=a.mutate, lanes=a.lanes)
     print("violations:", n)
     raise SystemExit(1 if n else 0)
