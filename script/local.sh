@@ -27,7 +27,20 @@ for ((i = 0; i < num_workers; ++i)); do
   ${bin} -my_node ${N} -scheduler ${Sch} ${arg} &
   pids+=($!)
 done
-wait ${sched_pid}
-rc=$?
-for p in "${pids[@]}"; do wait $p || rc=$?; done
+# Wait for every node.  A node that dies (a port already taken, a failed CHECK) would leave the
+# scheduler waiting for its registration forever: on the first non-zero exit stop the others.
+all=(${sched_pid} "${pids[@]}")
+rc=0
+left=${#all[@]}
+while [ ${left} -gt 0 ]; do
+  wait -n
+  st=$?
+  left=$((left - 1))
+  if [ ${st} -ne 0 ]; then
+    rc=${st}
+    kill "${all[@]}" 2>/dev/null
+    wait
+    break
+  fi
+done
 exit $rc

@@ -24,7 +24,7 @@ def _binaries():
 
 
 def _run(binary, servers, workers, *flags, timeout=180):
-    env = dict(os.environ, PS_BASE_PORT=str(random.randint(20000, 40000)))
+    env = dict(os.environ, PS_BASE_PORT=str(random.randint(10000, 30000)))
     r = subprocess.run([str(ROOT / "script" / "local.sh"), str(ROOT / "build" / binary), str(servers),
                         str(workers), *flags], cwd=ROOT, env=env, capture_output=True, text=True,
                        timeout=timeout)

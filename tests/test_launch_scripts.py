@@ -28,8 +28,31 @@ def _check_hello(out: str):
     }, out
 
 
+# Base ports stay below 30000: the nodes listen on base, base + 1500 + i and base + 1600 + i, and from
+# 32768 on a port may already belong to somebody's outgoing connection (the ephemeral range).
+
+
+def test_local_sh_stops_when_a_node_cannot_start():
+    """A node whose port is taken dies at start-up; the launcher must stop the other nodes and fail
+    instead of leaving the scheduler waiting for the missing registration (it used to hang)."""
+    import socket
+    import time
+    base = random.randint(10000, 30000)
+    blocker = socket.socket()
+    blocker.bind(("0.0.0.0", base + 1500))      # the port of worker W0
+    blocker.listen(1)
+    try:
+        t0 = time.time()
+        r = subprocess.run([str(ROOT / "script" / "local.sh"), str(HELLO), "1", "2"], cwd=ROOT,
+                           env=dict(os.environ, PS_BASE_PORT=str(base)), capture_output=True, text=True, timeout=60)
+        assert r.returncode != 0 and "cannot bind" in r.stderr, r.stdout + r.stderr
+        assert time.time() - t0 < 30
+    finally:
+        blocker.close()
+
+
 def test_local_sh_hello_world():
-    env = dict(os.environ, PS_BASE_PORT=str(random.randint(20000, 40000)))
+    env = dict(os.environ, PS_BASE_PORT=str(random.randint(10000, 30000)))
     r = subprocess.run([str(ROOT / "script" / "local.sh"), str(HELLO), "2", "2"], cwd=ROOT, env=env,
                        capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
@@ -38,7 +61,7 @@ def test_local_sh_hello_world():
 
 def test_mpi_node_sh_ranks_from_environment(tmp_path):
     """Every process gets the same command line; role, id, address and port come from its rank."""
-    port = random.randint(20000, 40000)
+    port = random.randint(10000, 30000)
     conf = tmp_path / "launch.conf"
     conf.write_text(f"bin={HELLO}\nnum_servers=1\nnum_workers=2\nnetwork_interface=\narg=\n")
     root = subprocess.run([str(ROOT / "script" / "get_root_node.sh"), "lo", str(port)],
@@ -114,7 +137,7 @@ def test_gzip_text_input(tmp_path):
 def test_observability_flags(tmp_path):
     """-print_van (message trace per node), -traffic_statistics (bytes at exit), -log_to_file
     (ref SURVEY 5.1 / 5.5: van.cc, postoffice.cc)"""
-    env = dict(os.environ, PS_BASE_PORT=str(random.randint(20000, 40000)))
+    env = dict(os.environ, PS_BASE_PORT=str(random.randint(10000, 30000)))
     r = subprocess.run([str(ROOT / "script" / "local.sh"), str(HELLO), "1", "2", "-print_van", "-traffic_statistics",
                         "-log_to_file"], cwd=tmp_path, env=env, capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
