@@ -162,6 +162,10 @@ def main(argv=None):
         if i == steps - 1 and m.n_rows:
             last["y"], last["xw"] = m.y.clone(), m.xw[:m.n_rows].clone()
 
+    from parameter_server_b200.utils.clocks import ClockSampler
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.passes + 1)]
     l0 = eng.launches
     wall0 = time.perf_counter()
@@ -179,6 +183,7 @@ def main(argv=None):
                          "accuracy": st[1] / max(st[2], 1.0),
                          "auc_last_minibatch": dev_auc(last["y"], last["xw"]) if last else float("nan")})
     wall = time.perf_counter() - wall0
+    clocks = sampler.stop() if sampler else None
     t = torch.tensor([ev[0].elapsed_time(ev[-1]), wall * 1e3, per_pass[0]["ms"],
                       sum(pp["ms"] for pp in per_pass[1:]) / max(len(per_pass) - 1, 1)], dtype=torch.float64, device=dev)
     tot = torch.tensor([float(total), float(data.nnz)], dtype=torch.float64, device=dev)
@@ -221,7 +226,7 @@ def main(argv=None):
             "e2e": {"value": tot[0].item() / (wall_ms / 1e3), "unit": "examples/s",
                     "h2d_bytes_per_step": eng.h2d_bytes / max(steps * args.passes, 1), "d2h_bytes_per_step": 32.0 / steps,
                     "api": "AsyncSGDEngine.train_stream"},
-            "gpu_launches": eng.launches - l0}))
+            "gpu_launches": eng.launches - l0, "clocks": clocks}))
     eng.close()
     if world > 1:
         dist.destroy_process_group()

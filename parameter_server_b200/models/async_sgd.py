@@ -34,7 +34,6 @@ import numpy as np
 import torch
 
 from .._lib import check, cuda_lib, current_stream, ptr
-from ..ops import localizer as L
 from ..ops._sig import apply_cuda_sigs
 from ..parallel.comm import Comm, SingleComm
 from ..utils.range import Range
