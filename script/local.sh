@@ -39,6 +39,8 @@ while [ ${left} -gt 0 ]; do
   if [ ${st} -ne 0 ]; then
     rc=${st}
     kill "${all[@]}" 2>/dev/null
+    sleep 1
+    kill -9 "${all[@]}" 2>/dev/null   # whoever ignored the first signal
     wait
     break
   fi
