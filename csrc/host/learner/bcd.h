@@ -311,7 +311,7 @@ class BCDServer : public BCDNode {
     for (int i = 0; i < at.groups; ++i) {  // the kept keys were joined into my key list
       model_.waitInMsg(kWorkerGroup, at.keys(i));
       const int chl = fea_grp_[i];
-      model_.clearTailFilter(chl);
+      model_.clearTailFilter(chl, i + 1 == at.groups);
       SArray<V>& w = model_.value(chl);
       w.resize(model_.key(chl).size());
       w.setValue(bcd_conf_.init_w());

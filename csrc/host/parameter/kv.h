@@ -117,7 +117,16 @@ class SharedParameter : public Customer {
 
   void setTailFilterIgnoreChl(bool flag) { one_filter_for_all_ = flag; }
   void setTailFilterSize(int chl, int n, int k) { tail_filter_[chl].resize(n, k); }
-  void clearTailFilter(int chl) { tail_filter_[one_filter_for_all_ ? 0 : chl].clear(); }
+  // Called by a server when the keys round of group `chl` is through.  With one sketch per channel that
+  // sketch is done.  With the shared sketch (the default, as in the reference) the count / query rounds
+  // of LATER groups may still be in flight at that moment, so only the last group's call clears it:
+  // by then every worker has pushed the keys of every group, i.e. all its queries have returned.
+  // (The reference clears key_filter_[chl] while its shared sketch lives at key 0 - shared_parameter.h:49,122 -
+  // so there the shared sketch is never cleared at all.)
+  void clearTailFilter(int chl, bool last_group) {
+    if (!one_filter_for_all_) tail_filter_[chl].clear();
+    else if (last_group) tail_filter_[0].clear();
+  }
 
   static CallSharedParaView set(MessagePtr msg) {
     msg->task.set_type(TaskView::CALL_CUSTOMER);

@@ -74,8 +74,8 @@ def test_shipped_ctr_batch_config_on_gpu(tmp_path):
     text, prior feature groups 127 / 120 swept first without delay, tail_feature_freq 4,
     max_block_delay 8 (9 blocks per device step).  Block orders are random and drawn from different
     generators on the two sides, so the trajectories differ; both must reach the same optimum.
-    OPEN (DESIGN.md section 7): failed twice on a box with two visible GPUs, never on a one-GPU box;
-    cause unknown, the failing values were not captured."""
+    (It failed on one box in round 2: the CPU half lost a whole feature group to a race in the servers'
+    shared tail filter - fixed, tests/test_host_apps.py::test_tail_filter_does_not_depend_on_timing_or_worker_count.)"""
     from parameter_server_b200.runtime import host
     from parameter_server_b200.utils.synthetic import make_ctr_like, write_ps_sparse_binary
     relabel = {1: 120, 2: 127, 3: 3, 4: 5}
