@@ -155,6 +155,7 @@ class InprocVan : public Van {
     MessagePtr m;
     inbox_->wait_and_pop(m);
     if (!m) return Status::Error("van closed");
+    jitter();
     size_t n = m->memSize();
     if (recv_bytes) *recv_bytes = n;
     countRecv(my_host_, n);
@@ -165,6 +166,19 @@ class InprocVan : public Van {
   void shutdown() override { if (inbox_) inbox_->push(MessagePtr()); }
 
  private:
+  // PSB_VAN_JITTER_US=n: every delivery waits a random 0..n microseconds first.  The order of one node's
+  // inbox is kept (as a real transport keeps the order of a connection); what changes is how the nodes
+  // interleave - which is what an ordering assumption between rounds of a protocol silently relies on
+  // (the shared tail-filter race of round 2 was one).  tests/test_host_apps.py runs the apps under it.
+  void jitter() {
+    static const int max_us = [] { const char* e = getenv("PSB_VAN_JITTER_US"); return e ? atoi(e) : 0; }();
+    if (max_us <= 0) return;
+    if (!rng_seeded_) { rng_state_ = std::hash<string>()(my_id_) | 1; rng_seeded_ = true; }
+    rng_state_ ^= rng_state_ << 13; rng_state_ ^= rng_state_ >> 7; rng_state_ ^= rng_state_ << 17;  // xorshift64
+    std::this_thread::sleep_for(std::chrono::microseconds((long)(rng_state_ % (uint64)(max_us + 1))));
+  }
+  uint64 rng_state_ = 0;
+  bool rng_seeded_ = false;
   shared_ptr<InprocFabric> fabric_;
   shared_ptr<InprocFabric::Queue> inbox_;
   std::mutex mu_;

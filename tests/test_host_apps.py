@@ -258,3 +258,19 @@ def test_shipped_rcv1_configs_train_then_evaluate(tmp_path, monkeypatch):
     # the shipped config sets no max_delay: how stale the gradients of the handful of minibatches
     # are depends on thread timing (typically auc ~0.89; all of them computed at w = 0 gives ~0.65)
     assert int(n) == 1200 and float(auc) > 0.6
+
+
+def test_apps_under_delivery_jitter():
+    """The same app tests with PSB_VAN_JITTER_US: every delivery of the in-process van waits a random
+    time first, so the nodes interleave differently from run to run while each inbox keeps its order.
+    An ordering assumption between the rounds of a protocol (such as the tail-filter race) shows up
+    here instead of on somebody else's machine.  Runs in a subprocess: the van reads the variable once."""
+    import subprocess
+    import sys
+    if os.environ.get("PSB_VAN_JITTER_US"):
+        pytest.skip("already running under jitter")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-p", "no:cacheprovider",
+                        "-k", "oracle or tail_filter or bounded_delay or ftrl_and_model_evaluation"],
+                       env=dict(os.environ, PSB_VAN_JITTER_US="400"), capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
+    assert " passed" in r.stdout and "failed" not in r.stdout
